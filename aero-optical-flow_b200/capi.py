@@ -1,0 +1,132 @@
+"""ctypes view of the C ABI in include/aof.h (libaof_b200.so).
+
+This is the binding a Python caller (tests, bench.py) uses; there is no other
+implementation behind it: if the library is missing or no CUDA device is
+present the calls raise, they never fall back to a CPU path.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libaof_b200.so")
+
+AOF_OK = 0
+AOF_ERR_BASE = -100
+AOF_PX4_MAX_BLOCKS = 25
+
+
+class AofError(RuntimeError):
+    pass
+
+
+class Px4Params(C.Structure):
+    _fields_ = [("focal_length_x", C.c_float), ("focal_length_y", C.c_float), ("output_rate", C.c_int),
+                ("image_width", C.c_int), ("image_height", C.c_int), ("search_size", C.c_int),
+                ("flow_feature_threshold", C.c_int), ("flow_value_threshold", C.c_int)]
+
+
+flow_out_dtype = np.dtype([("quality", np.int32), ("dt_us", np.int32), ("flow_x", np.float32),
+                           ("flow_y", np.float32)])
+px4_raw_dtype = np.dtype([("px_x", np.float32), ("px_y", np.float32), ("quality", np.int32), ("count", np.int32)])
+px4_block_dtype = np.dtype([("x", np.int16), ("y", np.int16), ("dx", np.int16), ("dy", np.int16),
+                            ("texture", np.uint32), ("best_sad", np.uint32), ("acc", np.uint32, (8,)),
+                            ("subdir", np.int32), ("accepted", np.int32)])
+
+_lib = None
+
+
+def lib():
+    """Load libaof_b200.so (built in-tree by build.sh / __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise AofError(f"{LIB_PATH} not built: run __graft_entry__.build() (no CPU fallback exists)")
+    L = C.CDLL(LIB_PATH)
+    vp, u8p, u32p, ip, fp = C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_float)
+    L.aof_version.restype = C.c_char_p
+    L.aof_last_error.restype = C.c_char_p
+    L.aof_device_count.restype = C.c_int
+    L.aof_launch_count.restype = C.c_uint64
+    L.aof_px4_default_params.argtypes = [C.POINTER(Px4Params)]
+    L.aof_px4_create.argtypes = [C.POINTER(Px4Params), C.c_int, C.c_int, C.POINTER(vp)]
+    L.aof_px4_destroy.argtypes = [vp]
+    L.aof_px4_destroy.restype = None
+    L.aof_px4_num_streams.argtypes = [vp]
+    L.aof_px4_reset.argtypes = [vp]
+    L.aof_px4_calc_flow.argtypes = [vp, u8p, C.c_uint32, ip, fp, fp]
+    L.aof_px4_calc_flow_batch.argtypes = [vp, u8p, u32p, vp]
+    L.aof_px4_calc_flow_device.argtypes = [vp, u8p, u32p, vp, vp, vp, vp]
+    L.aof_px4_compute_flow_pairs.argtypes = [vp, u8p, u8p, C.c_int, vp, vp]
+    L.aof_px4_compute_flow_pairs_device.argtypes = [vp, u8p, u8p, C.c_int, vp, vp, vp]
+    _lib = L
+    return L
+
+
+def check(rc, what=""):
+    if rc <= AOF_ERR_BASE:
+        raise AofError(f"{what} failed ({rc}): {lib().aof_last_error().decode()}")
+    return rc
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+class Px4Flow:
+    """n_streams OpticalFlowPX4 instances on one GPU (mirrors flow_px4.hpp:62-68)."""
+
+    def __init__(self, focal_x, focal_y, output_rate=15, width=64, height=64, search=6, feat_thr=30, val_thr=3000,
+                 n_streams=1, device=0):
+        L = lib()
+        self.params = Px4Params(focal_x, focal_y, output_rate, width, height, search, feat_thr, val_thr)
+        self.n, self.w, self.h = n_streams, width, height
+        self.handle = C.c_void_p()
+        check(L.aof_px4_create(C.byref(self.params), n_streams, device, C.byref(self.handle)), "aof_px4_create")
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib().aof_px4_destroy(self.handle)
+            self.handle = None
+
+    __del__ = close
+
+    def reset(self):
+        check(lib().aof_px4_reset(self.handle), "aof_px4_reset")
+
+    def calc_flow(self, img, t_us):
+        """One stream.  -> (quality, dt_us, flow_x, flow_y); outputs are None where untouched."""
+        img = np.ascontiguousarray(img, np.uint8)
+        assert img.size == self.w * self.h
+        dt = C.c_int(-123456); fx = C.c_float(np.nan); fy = C.c_float(np.nan)
+        q = check(lib().aof_px4_calc_flow(self.handle, _ptr(img), t_us, C.byref(dt), C.byref(fx), C.byref(fy)),
+                  "aof_px4_calc_flow")
+        return q, dt.value, fx.value, fy.value
+
+    def calc_flow_batch(self, imgs, t_us):
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        t_us = np.ascontiguousarray(t_us, np.uint32)
+        assert imgs.size == self.n * self.w * self.h and t_us.size == self.n
+        out = np.zeros(self.n, flow_out_dtype)
+        check(lib().aof_px4_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), _ptr(out)), "aof_px4_calc_flow_batch")
+        return out
+
+    def calc_flow_device(self, d_imgs, d_t_us, d_out, d_raw=0, d_blocks=0, stream=0):
+        """Raw device pointers (ints); asynchronous on `stream`."""
+        check(lib().aof_px4_calc_flow_device(self.handle, d_imgs, d_t_us, d_out, d_raw or None, d_blocks or None,
+                                             stream or None), "aof_px4_calc_flow_device")
+
+    def compute_flow_pairs(self, prev, cur, want_blocks=False):
+        prev = np.ascontiguousarray(prev, np.uint8); cur = np.ascontiguousarray(cur, np.uint8)
+        n = prev.size // (self.w * self.h)
+        raw = np.zeros(n, px4_raw_dtype)
+        blocks = np.zeros((n, AOF_PX4_MAX_BLOCKS), px4_block_dtype) if want_blocks else None
+        check(lib().aof_px4_compute_flow_pairs(self.handle, _ptr(prev), _ptr(cur), n, _ptr(raw),
+                                               _ptr(blocks) if want_blocks else None), "aof_px4_compute_flow_pairs")
+        return (raw, blocks) if want_blocks else raw
+
+    def compute_flow_pairs_device(self, d_prev, d_cur, n, d_raw, d_blocks=0, stream=0):
+        check(lib().aof_px4_compute_flow_pairs_device(self.handle, d_prev, d_cur, n, d_raw, d_blocks or None,
+                                                      stream or None), "aof_px4_compute_flow_pairs_device")

@@ -1,0 +1,22 @@
+// Host-only helpers for the C-ABI translation units.
+#pragma once
+#include <cstdarg>
+#include <cuda_runtime.h>
+
+#include "../../include/aof.h"
+
+namespace aof {
+void set_error(const char *fmt, ...);
+const char *last_error();
+int select_device(int device);
+} // namespace aof
+
+// CUDA errors never cross the ABI as exceptions: record the text, return a code
+#define AOF_CUDA(expr)                                                                         \
+	do {                                                                                   \
+		cudaError_t _e = (expr);                                                       \
+		if (_e != cudaSuccess) {                                                       \
+			aof::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+			return AOF_ERR_CUDA;                                                   \
+		}                                                                              \
+	} while (0)
