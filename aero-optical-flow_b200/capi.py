@@ -34,6 +34,15 @@ px4_block_dtype = np.dtype([("x", np.int16), ("y", np.int16), ("dx", np.int16), 
                             ("texture", np.uint32), ("best_sad", np.uint32), ("acc", np.uint32, (8,)),
                             ("subdir", np.int32), ("accepted", np.int32)])
 
+class LkParams(C.Structure):
+    _fields_ = [("focal_length_x", C.c_float), ("focal_length_y", C.c_float), ("output_rate", C.c_int),
+                ("image_width", C.c_int), ("image_height", C.c_int), ("num_features", C.c_int),
+                ("confidence_multiplier", C.c_float)]
+
+
+lk_raw_dtype = np.dtype([("px_x", np.float32), ("px_y", np.float32), ("inliers", np.int32), ("active", np.int32),
+                         ("fast_bins", np.int32), ("quality", np.int32)])
+
 _lib = None
 
 
@@ -61,6 +70,19 @@ def lib():
     L.aof_px4_calc_flow_device.argtypes = [vp, u8p, u32p, vp, vp, vp, vp]
     L.aof_px4_compute_flow_pairs.argtypes = [vp, u8p, u8p, C.c_int, vp, vp]
     L.aof_px4_compute_flow_pairs_device.argtypes = [vp, u8p, u8p, C.c_int, vp, vp, vp]
+    L.aof_lk_default_params.argtypes = [C.POINTER(LkParams)]
+    L.aof_lk_create.argtypes = [C.POINTER(LkParams), C.c_int, C.c_int, C.POINTER(vp)]
+    L.aof_lk_destroy.argtypes = [vp]
+    L.aof_lk_destroy.restype = None
+    L.aof_lk_num_streams.argtypes = [vp]
+    L.aof_lk_reset.argtypes = [vp]
+    L.aof_lk_calc_flow.argtypes = [vp, u8p, C.c_uint32, ip, fp, fp]
+    L.aof_lk_calc_flow_batch.argtypes = [vp, u8p, u32p, vp, vp]
+    L.aof_lk_calc_flow_device.argtypes = [vp, u8p, u32p, vp, vp, vp]
+    L.aof_lk_get_state.argtypes = [vp, vp, vp, vp, vp]
+    L.aof_lk_pyramid.argtypes = [vp, u8p, C.c_int, vp, vp, vp]
+    L.aof_lk_track_points.argtypes = [vp, u8p, u8p, C.c_int, vp, C.c_int, vp, vp]
+    L.aof_lk_fast_scores.argtypes = [vp, u8p, C.c_int, vp]
     _lib = L
     return L
 
@@ -130,3 +152,87 @@ class Px4Flow:
     def compute_flow_pairs_device(self, d_prev, d_cur, n, d_raw, d_blocks=0, stream=0):
         check(lib().aof_px4_compute_flow_pairs_device(self.handle, d_prev, d_cur, n, d_raw, d_blocks or None,
                                                       stream or None), "aof_px4_compute_flow_pairs_device")
+
+
+class LkFlow:
+    """n_streams OpticalFlowOpenCV instances on one GPU (mirrors flow_opencv.hpp:73-88)."""
+
+    def __init__(self, focal_x, focal_y, output_rate=15, width=64, height=64, num_features=20, conf_multi=1.645,
+                 n_streams=1, device=0):
+        L = lib()
+        self.params = LkParams(focal_x, focal_y, output_rate, width, height, num_features, conf_multi)
+        self.n, self.w, self.h, self.nf = n_streams, width, height, num_features
+        self.handle = C.c_void_p()
+        check(L.aof_lk_create(C.byref(self.params), n_streams, device, C.byref(self.handle)), "aof_lk_create")
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib().aof_lk_destroy(self.handle)
+            self.handle = None
+
+    __del__ = close
+
+    def reset(self):
+        check(lib().aof_lk_reset(self.handle), "aof_lk_reset")
+
+    def calc_flow(self, img, t_us):
+        img = np.ascontiguousarray(img, np.uint8)
+        assert img.size == self.w * self.h
+        dt = C.c_int(-123456); fx = C.c_float(np.nan); fy = C.c_float(np.nan)
+        q = check(lib().aof_lk_calc_flow(self.handle, _ptr(img), int(t_us), C.byref(dt), C.byref(fx), C.byref(fy)),
+                  "aof_lk_calc_flow")
+        return q, dt.value, fx.value, fy.value
+
+    def calc_flow_batch(self, imgs, t_us, want_raw=False):
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        t_us = np.ascontiguousarray(t_us, np.uint32)
+        assert imgs.size == self.n * self.w * self.h and t_us.size == self.n
+        out = np.zeros(self.n, flow_out_dtype)
+        raw = np.zeros(self.n, lk_raw_dtype) if want_raw else None
+        check(lib().aof_lk_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), _ptr(out),
+                                           _ptr(raw) if want_raw else None), "aof_lk_calc_flow_batch")
+        return (out, raw) if want_raw else out
+
+    def calc_flow_device(self, d_imgs, d_t_us, d_out, d_raw=0, stream=0):
+        check(lib().aof_lk_calc_flow_device(self.handle, d_imgs, d_t_us, d_out, d_raw or None, stream or None),
+              "aof_lk_calc_flow_device")
+
+    def state(self):
+        uv = np.zeros((self.n, self.nf), np.int32)
+        fc = np.zeros((self.n, self.nf, 2), np.float32)
+        pc = np.zeros((self.n, self.nf, 2), np.float32)
+        ps = np.zeros((self.n, self.nf), np.uint8)
+        check(lib().aof_lk_get_state(self.handle, _ptr(uv), _ptr(fc), _ptr(pc), _ptr(ps)), "aof_lk_get_state")
+        return {"update_vec": uv, "feat_cur": fc, "prev_corners": pc, "prev_status": ps}
+
+    def pyramid(self, imgs):
+        imgs = np.ascontiguousarray(imgs, np.uint8).reshape(-1, self.h, self.w)
+        n = len(imgs)
+        lw = np.zeros(4, np.int32); lh = np.zeros(4, np.int32)
+        nl = check(lib().aof_lk_pyramid(self.handle, None, 0, _ptr(lw), _ptr(lh), None), "aof_lk_pyramid")
+        per = int(sum(int(lw[l]) * int(lh[l]) for l in range(nl)))
+        buf = np.zeros((n, per), np.uint8)
+        check(lib().aof_lk_pyramid(self.handle, _ptr(imgs), n, _ptr(lw), _ptr(lh), _ptr(buf)), "aof_lk_pyramid")
+        levels, o = [], 0
+        for l in range(nl):
+            sz = int(lw[l]) * int(lh[l])
+            levels.append(buf[:, o:o + sz].reshape(n, int(lh[l]), int(lw[l])))
+            o += sz
+        return levels
+
+    def track_points(self, prev, cur, pts):
+        prev = np.ascontiguousarray(prev, np.uint8).reshape(-1, self.h, self.w)
+        cur = np.ascontiguousarray(cur, np.uint8).reshape(-1, self.h, self.w)
+        n = len(prev)
+        pts = np.ascontiguousarray(pts, np.float32).reshape(n, -1, 2)
+        out = np.zeros_like(pts)
+        st = np.zeros(pts.shape[:2], np.uint8)
+        check(lib().aof_lk_track_points(self.handle, _ptr(prev), _ptr(cur), n, _ptr(pts), pts.shape[1], _ptr(out),
+                                        _ptr(st)), "aof_lk_track_points")
+        return out, st
+
+    def fast_scores(self, imgs):
+        imgs = np.ascontiguousarray(imgs, np.uint8).reshape(-1, self.h, self.w)
+        sc = np.zeros_like(imgs)
+        check(lib().aof_lk_fast_scores(self.handle, _ptr(imgs), len(imgs), _ptr(sc)), "aof_lk_fast_scores")
+        return sc

@@ -9,6 +9,9 @@ namespace aof {
 void set_error(const char *fmt, ...);
 const char *last_error();
 int select_device(int device);
+// host -> device copy of `bytes` on `st`: directly if `src` is pinned (cudaHostAlloc / cudaHostRegister),
+// else through the pinned staging buffer `stage` (>= bytes) in chunks so the CPU copy overlaps the DMA
+int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStream_t st);
 } // namespace aof
 
 // CUDA errors never cross the ABI as exceptions: record the text, return a code

@@ -66,3 +66,57 @@ cudaError_t px4_epilogue_launch(const aof_px4_raw *raw, const uint32_t *t_us, Li
 				int n, int output_rate, float fx, float fy, cudaStream_t st);
 
 } // namespace aof
+
+// ---------------------------------------------------------------------------
+// LK path (OpticalFlowOpenCV::calcFlow, trackFeatures, calcOpticalFlowPyrLK, FAST)
+namespace aof {
+
+constexpr int LK_MAX_LEVELS = 4;   // maxLevel = 3 (trackFeatures.cpp:98)
+constexpr int LK_WIN = 9;          // Size(9, 9)
+constexpr int LK_MAX_FEATURES = 100; // trackFeatures.cpp:56
+constexpr int LK_BINS = 16;        // 4 x 4 (trackFeatures.cpp:156-157)
+
+struct LkGeom {
+	int w[LK_MAX_LEVELS], h[LK_MAX_LEVELS];
+	int top;          // index of the coarsest level (OpenCV stops when the next one would be <= the window)
+	int n_feat;       // N = updateVector.size()
+	int bw, bh;       // bin size (cols/4, rows/4)
+	int tpb;          // targetFeaturesPerBin
+	int dist;         // binWidth / targetFeaturesPerBin
+	int kp_cap;       // keypoint-list capacity per bin
+	int fast_thr;     // 10
+};
+
+// level base pointers of one pyramid slot; level l of stream s is at lvl[l] + s * w[l] * h[l]
+struct LkPyr {
+	const uint8_t *lvl[LK_MAX_LEVELS];
+};
+
+// per-stream tracker state, structure of arrays over n_streams
+struct LkState {
+	float2 *prev_corners;   // [n * N]   trackFeatures.cpp:54
+	uint8_t *prev_status;   // [n * N]   :56
+	int *n_prev_corners;    // [n]       prev_corners.size(): 0 or N
+	int *update_vec;        // [n * N]   flow_opencv.hpp:66
+	float2 *feat_cur;       // [n * N]   features_current
+	float2 *feat_prev;      // [n * N]   features_previous
+	LimiterState *lim;      // [n]
+	int *bin_needed;        // [n * 16]  neededFeatures per bin (bin = x * 4 + y)
+	int *target;            // [n]       targetNumPoints
+	int *kp_count;          // [n * 16]
+	uint32_t *kp;           // [n * 16 * kp_cap]  score << 24 | bin-local raster index
+};
+
+cudaError_t lk_pyr_down_launch(const uint8_t *src, uint8_t *dst, int sw, int sh, int n, cudaStream_t st);
+cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
+				   int have_prev, cudaStream_t st);
+cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map,
+			   cudaStream_t st);
+cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
+				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
+				      float fy, cudaStream_t st);
+// stateless pyramidal LK over given points (KAT entry): pts[n * n_pts]
+cudaError_t lk_track_points_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const float2 *pts, int n_pts,
+				   float2 *out, uint8_t *status, int n, cudaStream_t st);
+
+} // namespace aof

@@ -1,0 +1,372 @@
+// C-ABI host side of the LK path (include/aof.h): per-stream device state, pinned
+// staging, async copies, launches.  Replaces the host logic of OpticalFlowOpenCV
+// (src/flow_opencv.cpp:47-210) and of trackFeatures' file statics
+// (external/klt_feature_tracker/src/trackFeatures.cpp:53-56); the arithmetic is in
+// lk_kernels.cu.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "aof_internal.h"
+#include "aof_host.h"
+
+using namespace aof;
+
+struct aof_lk {
+	aof_lk_params p;
+	int n = 0, device = 0;
+	LkGeom g{};
+	cudaStream_t st = nullptr;
+	size_t lvl_px[LK_MAX_LEVELS] = {};   // pixels of one frame at level l
+	size_t upper_off[LK_MAX_LEVELS] = {}; // offset of the level-l block (l >= 1) inside d_upper[slot]
+	size_t upper_bytes = 0;
+	uint8_t *d_upper[2] = {nullptr, nullptr};
+	const uint8_t *l0[2] = {nullptr, nullptr};
+	int cur = 0;
+	bool have_prev = false, have_feat_prev = false;
+	LkState s{};
+	// host-batch path (allocated on first use)
+	uint8_t *d_frames[2] = {nullptr, nullptr};
+	uint8_t *h_stage = nullptr;
+	uint32_t *h_t = nullptr, *d_t = nullptr;
+	aof_flow_out *h_out = nullptr, *d_out = nullptr;
+	aof_lk_raw *h_raw = nullptr, *d_raw = nullptr;
+};
+
+static LkPyr pyr_of(const aof_lk *h, int slot)
+{
+	LkPyr p{};
+	p.lvl[0] = h->l0[slot];
+	for (int l = 1; l <= h->g.top; l++) p.lvl[l] = h->d_upper[slot] + h->upper_off[l];
+	return p;
+}
+
+// levels 1..top of n frames whose level 0 is at l0; level blocks at upper + off[l]
+static cudaError_t build_upper(const LkGeom &g, const uint8_t *l0, uint8_t *upper, const size_t *off, int n, cudaStream_t st)
+{
+	for (int l = 1; l <= g.top; l++) {
+		const uint8_t *src = l == 1 ? l0 : upper + off[l - 1];
+		cudaError_t e = lk_pyr_down_launch(src, upper + off[l], g.w[l - 1], g.h[l - 1], n, st);
+		if (e != cudaSuccess) return e;
+	}
+	return cudaSuccess;
+}
+
+static int reset_state(aof_lk *h)
+{
+	const size_t nN = (size_t)h->n * h->g.n_feat;
+	std::vector<int> twos(nN, 2);
+	AOF_CUDA(cudaMemcpy(h->s.update_vec, twos.data(), sizeof(int) * nN, cudaMemcpyHostToDevice));
+	AOF_CUDA(cudaMemset(h->s.prev_corners, 0, sizeof(float2) * nN));
+	AOF_CUDA(cudaMemset(h->s.prev_status, 0, nN));
+	AOF_CUDA(cudaMemset(h->s.n_prev_corners, 0, sizeof(int) * h->n));
+	AOF_CUDA(cudaMemset(h->s.feat_cur, 0, sizeof(float2) * nN));
+	AOF_CUDA(cudaMemset(h->s.feat_prev, 0, sizeof(float2) * nN));
+	AOF_CUDA(cudaMemset(h->s.lim, 0, sizeof(LimiterState) * h->n));
+	AOF_CUDA(cudaMemset(h->s.bin_needed, 0, sizeof(int) * LK_BINS * h->n));
+	AOF_CUDA(cudaMemset(h->s.target, 0, sizeof(int) * h->n));
+	AOF_CUDA(cudaMemset(h->s.kp_count, 0, sizeof(int) * LK_BINS * h->n));
+	h->have_prev = h->have_feat_prev = false;
+	h->cur = 0;
+	h->l0[0] = h->l0[1] = nullptr;
+	return AOF_OK;
+}
+
+extern "C" {
+
+void aof_lk_default_params(aof_lk_params *p)
+{
+	if (!p) return;
+	p->focal_length_x = p->focal_length_y = 0.f;
+	p->output_rate = 15;              // include/optical_flow.hpp:47
+	p->image_width = 64;              // :48
+	p->image_height = 64;             // :49
+	p->num_features = 20;             // include/flow_opencv.hpp:53
+	p->confidence_multiplier = 1.645f; // :54
+}
+
+int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **out)
+{
+	if (!p || !out || n_streams < 1) { set_error("aof_lk_create: bad argument"); return AOF_ERR_INVALID; }
+	*out = nullptr;
+	const int W = p->image_width, H = p->image_height, N = p->num_features;
+	if (N < 1 || N > LK_MAX_FEATURES) { set_error("num_features %d outside 1..%d (trackFeatures.cpp:56)", N, LK_MAX_FEATURES); return AOF_ERR_UNSUPPORTED; }
+	const int tpb = (N - 1) / LK_BINS + 1;
+	if (W < 16 || H < 16 || (W / 4) / tpb < 2 || n_streams > 65535) {
+		set_error("image %dx%d / %d features / %d streams unsupported (need W,H >= 16, (W/4)/ceil(N/16) >= 2, streams <= 65535)", W, H, N, n_streams);
+		return AOF_ERR_UNSUPPORTED;
+	}
+	int rc = select_device(device);
+	if (rc != AOF_OK) return rc;
+	aof_lk *h = new (std::nothrow) aof_lk();
+	if (!h) return AOF_ERR_INVALID;
+	h->p = *p; h->n = n_streams; h->device = device;
+	LkGeom &g = h->g;
+	g.n_feat = N; g.bw = W / 4; g.bh = H / 4; g.tpb = tpb; g.dist = g.bw / tpb; g.fast_thr = 10;
+	g.kp_cap = ((g.bw + 1) / 2) * ((g.bh + 1) / 2);
+	// cv::buildOpticalFlowPyramid: stop when the next level would be <= the window
+	int lw = W, lh = H, level = 0;
+	g.w[0] = W; g.h[0] = H;
+	for (; level < LK_MAX_LEVELS - 1; level++) {
+		const int nw = (lw + 1) / 2, nh = (lh + 1) / 2;
+		if (nw <= LK_WIN || nh <= LK_WIN) break;
+		lw = nw; lh = nh;
+		g.w[level + 1] = lw; g.h[level + 1] = lh;
+	}
+	g.top = level;
+	size_t off = 0;
+	for (int l = 0; l <= g.top; l++) {
+		h->lvl_px[l] = (size_t)g.w[l] * g.h[l];
+		if (l >= 1) { h->upper_off[l] = off; off += (h->lvl_px[l] * n_streams + 255) & ~(size_t)255; }
+	}
+	h->upper_bytes = off ? off : 256;
+	const size_t nN = (size_t)n_streams * N;
+	cudaError_t e;
+	if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->d_upper[0], h->upper_bytes)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->d_upper[1], h->upper_bytes)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.prev_corners, sizeof(float2) * nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.prev_status, nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.n_prev_corners, sizeof(int) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.update_vec, sizeof(int) * nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.feat_cur, sizeof(float2) * nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.feat_prev, sizeof(float2) * nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lim, sizeof(LimiterState) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.bin_needed, sizeof(int) * LK_BINS * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.target, sizeof(int) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.kp_count, sizeof(int) * LK_BINS * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.kp, sizeof(uint32_t) * LK_BINS * (size_t)g.kp_cap * n_streams)) != cudaSuccess) {
+		set_error("aof_lk_create: %s", cudaGetErrorString(e));
+		aof_lk_destroy(h);
+		return AOF_ERR_CUDA;
+	}
+	rc = reset_state(h);
+	if (rc != AOF_OK) { aof_lk_destroy(h); return rc; }
+	*out = h;
+	return AOF_OK;
+}
+
+void aof_lk_destroy(aof_lk *h)
+{
+	if (!h) return;
+	cudaSetDevice(h->device);
+	if (h->st) cudaStreamSynchronize(h->st);
+	cudaFree(h->d_upper[0]); cudaFree(h->d_upper[1]);
+	cudaFree(h->s.prev_corners); cudaFree(h->s.prev_status); cudaFree(h->s.n_prev_corners); cudaFree(h->s.update_vec);
+	cudaFree(h->s.feat_cur); cudaFree(h->s.feat_prev); cudaFree(h->s.lim); cudaFree(h->s.bin_needed);
+	cudaFree(h->s.target); cudaFree(h->s.kp_count); cudaFree(h->s.kp);
+	cudaFree(h->d_frames[0]); cudaFree(h->d_frames[1]);
+	cudaFreeHost(h->h_stage); cudaFreeHost(h->h_t); cudaFreeHost(h->h_out); cudaFreeHost(h->h_raw);
+	cudaFree(h->d_t); cudaFree(h->d_out); cudaFree(h->d_raw);
+	if (h->st) cudaStreamDestroy(h->st);
+	delete h;
+}
+
+int aof_lk_num_streams(const aof_lk *h) { return h ? h->n : AOF_ERR_INVALID; }
+
+int aof_lk_reset(aof_lk *h)
+{
+	if (!h) return AOF_ERR_INVALID;
+	AOF_CUDA(cudaSetDevice(h->device));
+	AOF_CUDA(cudaStreamSynchronize(h->st));
+	AOF_CUDA(cudaDeviceSynchronize());
+	return reset_state(h);
+}
+
+int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
+			    aof_lk_raw *d_raw, void *cuda_stream)
+{
+	if (!h || !d_imgs || !d_t_us || !d_out) { set_error("lk calc_flow_device: null argument"); return AOF_ERR_INVALID; }
+	AOF_CUDA(cudaSetDevice(h->device));
+	cudaStream_t st = (cudaStream_t)cuda_stream;
+	const int nxt = h->cur ^ 1;
+	h->l0[nxt] = d_imgs;
+	AOF_CUDA(build_upper(h->g, d_imgs, h->d_upper[nxt], h->upper_off, h->n, st));
+	const LkPyr next = pyr_of(h, nxt);
+	const LkPyr prev = h->have_prev ? pyr_of(h, h->cur) : next;
+	AOF_CUDA(lk_track_update_launch(h->g, prev, next, h->s, h->n, h->have_prev ? 1 : 0, st));
+	AOF_CUDA(lk_fast_launch(h->g, d_imgs, h->s, h->n, nullptr, st));
+	AOF_CUDA(lk_select_epilogue_launch(h->g, h->s, d_t_us, d_out, d_raw, h->n, h->have_feat_prev ? 1 : 0,
+					   h->p.output_rate, h->p.confidence_multiplier, h->p.focal_length_x,
+					   h->p.focal_length_y, st));
+	h->cur = nxt;
+	h->have_prev = h->have_feat_prev = true;
+	return AOF_OK;
+}
+
+static int ensure_batch_buffers(aof_lk *h)
+{
+	if (h->h_stage) return AOF_OK;
+	const size_t fb = h->lvl_px[0] * h->n;
+	AOF_CUDA(cudaMalloc(&h->d_frames[0], fb));
+	AOF_CUDA(cudaMalloc(&h->d_frames[1], fb));
+	AOF_CUDA(cudaMallocHost(&h->h_t, sizeof(uint32_t) * h->n));
+	AOF_CUDA(cudaMallocHost(&h->h_out, sizeof(aof_flow_out) * h->n));
+	AOF_CUDA(cudaMallocHost(&h->h_raw, sizeof(aof_lk_raw) * h->n));
+	AOF_CUDA(cudaMalloc(&h->d_t, sizeof(uint32_t) * h->n));
+	AOF_CUDA(cudaMalloc(&h->d_out, sizeof(aof_flow_out) * h->n));
+	AOF_CUDA(cudaMalloc(&h->d_raw, sizeof(aof_lk_raw) * h->n));
+	AOF_CUDA(cudaMallocHost(&h->h_stage, fb));
+	return AOF_OK;
+}
+
+int aof_lk_calc_flow_batch(aof_lk *h, const uint8_t *imgs, const uint32_t *t_us, aof_flow_out *out, aof_lk_raw *raw)
+{
+	if (!h || !imgs || !t_us || !out) { set_error("lk calc_flow_batch: null argument"); return AOF_ERR_INVALID; }
+	AOF_CUDA(cudaSetDevice(h->device));
+	int rc = ensure_batch_buffers(h);
+	if (rc != AOF_OK) return rc;
+	const size_t total = h->lvl_px[0] * h->n;
+	uint8_t *d_cur = h->d_frames[h->cur ^ 1];
+	rc = stage_h2d(d_cur, imgs, total, h->h_stage, h->st);
+	if (rc != AOF_OK) return rc;
+	memcpy(h->h_t, t_us, sizeof(uint32_t) * h->n);
+	AOF_CUDA(cudaMemcpyAsync(h->d_t, h->h_t, sizeof(uint32_t) * h->n, cudaMemcpyHostToDevice, h->st));
+	rc = aof_lk_calc_flow_device(h, d_cur, h->d_t, h->d_out, h->d_raw, h->st);
+	if (rc != AOF_OK) return rc;
+	AOF_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
+	if (raw) AOF_CUDA(cudaMemcpyAsync(h->h_raw, h->d_raw, sizeof(aof_lk_raw) * h->n, cudaMemcpyDeviceToHost, h->st));
+	AOF_CUDA(cudaStreamSynchronize(h->st));
+	memcpy(out, h->h_out, sizeof(aof_flow_out) * h->n);
+	if (raw) memcpy(raw, h->h_raw, sizeof(aof_lk_raw) * h->n);
+	return AOF_OK;
+}
+
+int aof_lk_calc_flow(aof_lk *h, const uint8_t *img, uint32_t img_time_us, int *dt_us, float *flow_x, float *flow_y)
+{
+	if (!h || !img || !dt_us || !flow_x || !flow_y) { set_error("lk calc_flow: null argument"); return AOF_ERR_INVALID; }
+	if (h->n != 1) { set_error("calc_flow needs a 1-stream handle (this one has %d)", h->n); return AOF_ERR_STATE; }
+	aof_flow_out o;
+	int rc = aof_lk_calc_flow_batch(h, img, &img_time_us, &o, nullptr);
+	if (rc != AOF_OK) return rc;
+	*flow_x = o.flow_x;
+	*flow_y = o.flow_y;
+	if (o.quality >= 0 || h->p.output_rate <= 0) *dt_us = o.dt_us;
+	return o.quality;
+}
+
+int aof_lk_get_state(aof_lk *h, int32_t *update_vec, float *feat_cur, float *prev_corners, uint8_t *prev_status)
+{
+	if (!h) return AOF_ERR_INVALID;
+	AOF_CUDA(cudaSetDevice(h->device));
+	AOF_CUDA(cudaDeviceSynchronize());
+	const size_t nN = (size_t)h->n * h->g.n_feat;
+	if (update_vec) AOF_CUDA(cudaMemcpy(update_vec, h->s.update_vec, sizeof(int) * nN, cudaMemcpyDeviceToHost));
+	if (feat_cur) AOF_CUDA(cudaMemcpy(feat_cur, h->s.feat_cur, sizeof(float2) * nN, cudaMemcpyDeviceToHost));
+	if (prev_corners) AOF_CUDA(cudaMemcpy(prev_corners, h->s.prev_corners, sizeof(float2) * nN, cudaMemcpyDeviceToHost));
+	if (prev_status) AOF_CUDA(cudaMemcpy(prev_status, h->s.prev_status, nN, cudaMemcpyDeviceToHost));
+	return AOF_OK;
+}
+
+} // extern "C"
+
+// ---- kernel-level entry points for known-answer tests (host pointers, synchronous) ----
+
+namespace {
+struct TmpPyr { // pyramids of n frames in scratch device memory
+	uint8_t *l0 = nullptr, *upper = nullptr;
+	size_t off[LK_MAX_LEVELS] = {};
+	~TmpPyr() { cudaFree(l0); cudaFree(upper); }
+};
+
+int make_tmp_pyr(aof_lk *h, const uint8_t *imgs, int n, TmpPyr &t)
+{
+	const LkGeom &g = h->g;
+	size_t o = 0;
+	for (int l = 1; l <= g.top; l++) { t.off[l] = o; o += (h->lvl_px[l] * n + 255) & ~(size_t)255; }
+	AOF_CUDA(cudaMalloc(&t.l0, h->lvl_px[0] * n));
+	AOF_CUDA(cudaMalloc(&t.upper, o ? o : 256));
+	AOF_CUDA(cudaMemcpyAsync(t.l0, imgs, h->lvl_px[0] * n, cudaMemcpyHostToDevice, h->st));
+	AOF_CUDA(build_upper(g, t.l0, t.upper, t.off, n, h->st));
+	return AOF_OK;
+}
+
+LkPyr pyr_of_tmp(const LkGeom &g, const TmpPyr &t)
+{
+	LkPyr p{};
+	p.lvl[0] = t.l0;
+	for (int l = 1; l <= g.top; l++) p.lvl[l] = t.upper + t.off[l];
+	return p;
+}
+} // namespace
+
+extern "C" {
+
+int aof_lk_pyramid(aof_lk *h, const uint8_t *imgs, int n, int *lw, int *lh, uint8_t *levels)
+{
+	if (!h || n < 0 || n > 65535) { set_error("aof_lk_pyramid: bad argument"); return AOF_ERR_INVALID; }
+	const LkGeom &g = h->g;
+	for (int l = 0; l <= g.top; l++) { if (lw) lw[l] = g.w[l]; if (lh) lh[l] = g.h[l]; }
+	if (!levels || !imgs || n == 0) return g.top + 1;
+	AOF_CUDA(cudaSetDevice(h->device));
+	TmpPyr t;
+	int rc = make_tmp_pyr(h, imgs, n, t);
+	if (rc != AOF_OK) return rc;
+	size_t per_frame = 0;
+	for (int l = 0; l <= g.top; l++) per_frame += h->lvl_px[l];
+	size_t lo = 0;
+	for (int l = 0; l <= g.top; l++) { // strided copy: level l of frame i -> levels + i * per_frame + lo
+		const uint8_t *src = l == 0 ? t.l0 : t.upper + t.off[l];
+		AOF_CUDA(cudaMemcpy2DAsync(levels + lo, per_frame, src, h->lvl_px[l], h->lvl_px[l], n, cudaMemcpyDeviceToHost, h->st));
+		lo += h->lvl_px[l];
+	}
+	AOF_CUDA(cudaStreamSynchronize(h->st));
+	return g.top + 1;
+}
+
+int aof_lk_track_points(aof_lk *h, const uint8_t *prev, const uint8_t *cur, int n, const float *pts, int n_pts,
+			float *next_pts, uint8_t *status)
+{
+	if (!h || !prev || !cur || !pts || !next_pts || !status || n < 0 || n > 65535 || n_pts < 0) {
+		set_error("aof_lk_track_points: bad argument");
+		return AOF_ERR_INVALID;
+	}
+	if (n == 0 || n_pts == 0) return AOF_OK;
+	AOF_CUDA(cudaSetDevice(h->device));
+	TmpPyr a, b;
+	int rc = make_tmp_pyr(h, prev, n, a);
+	if (rc != AOF_OK) return rc;
+	rc = make_tmp_pyr(h, cur, n, b);
+	if (rc != AOF_OK) return rc;
+	const size_t np = (size_t)n * n_pts;
+	float2 *d_pts = nullptr, *d_out = nullptr;
+	uint8_t *d_st = nullptr;
+	cudaError_t e;
+	if ((e = cudaMalloc(&d_pts, sizeof(float2) * np)) != cudaSuccess || (e = cudaMalloc(&d_out, sizeof(float2) * np)) != cudaSuccess ||
+	    (e = cudaMalloc(&d_st, np)) != cudaSuccess ||
+	    (e = cudaMemcpyAsync(d_pts, pts, sizeof(float2) * np, cudaMemcpyHostToDevice, h->st)) != cudaSuccess ||
+	    (e = lk_track_points_launch(h->g, pyr_of_tmp(h->g, a), pyr_of_tmp(h->g, b), d_pts, n_pts, d_out, d_st, n, h->st)) != cudaSuccess ||
+	    (e = cudaMemcpyAsync(next_pts, d_out, sizeof(float2) * np, cudaMemcpyDeviceToHost, h->st)) != cudaSuccess ||
+	    (e = cudaMemcpyAsync(status, d_st, np, cudaMemcpyDeviceToHost, h->st)) != cudaSuccess ||
+	    (e = cudaStreamSynchronize(h->st)) != cudaSuccess) {
+		set_error("aof_lk_track_points: %s", cudaGetErrorString(e));
+		rc = AOF_ERR_CUDA;
+	}
+	cudaFree(d_pts); cudaFree(d_out); cudaFree(d_st);
+	return rc;
+}
+
+int aof_lk_fast_scores(aof_lk *h, const uint8_t *imgs, int n, uint8_t *score)
+{
+	if (!h || !imgs || !score || n < 0 || n > 65535) { set_error("aof_lk_fast_scores: bad argument"); return AOF_ERR_INVALID; }
+	if (n == 0) return AOF_OK;
+	AOF_CUDA(cudaSetDevice(h->device));
+	const size_t bytes = h->lvl_px[0] * n;
+	uint8_t *d_img = nullptr, *d_sc = nullptr;
+	int rc = AOF_OK;
+	cudaError_t e;
+	if ((e = cudaMalloc(&d_img, bytes)) != cudaSuccess || (e = cudaMalloc(&d_sc, bytes)) != cudaSuccess ||
+	    (e = cudaMemcpyAsync(d_img, imgs, bytes, cudaMemcpyHostToDevice, h->st)) != cudaSuccess ||
+	    (e = cudaMemsetAsync(d_sc, 0, bytes, h->st)) != cudaSuccess ||
+	    (e = lk_fast_launch(h->g, d_img, h->s, n, d_sc, h->st)) != cudaSuccess ||
+	    (e = cudaMemcpyAsync(score, d_sc, bytes, cudaMemcpyDeviceToHost, h->st)) != cudaSuccess ||
+	    (e = cudaStreamSynchronize(h->st)) != cudaSuccess) {
+		set_error("aof_lk_fast_scores: %s", cudaGetErrorString(e));
+		rc = AOF_ERR_CUDA;
+	}
+	cudaFree(d_img); cudaFree(d_sc);
+	return rc;
+}
+
+} // extern "C"

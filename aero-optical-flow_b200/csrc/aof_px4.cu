@@ -35,6 +35,24 @@ int select_device(int device)
 	return AOF_OK;
 }
 
+int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStream_t st)
+{
+	cudaPointerAttributes at{};
+	const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+	cudaGetLastError();
+	if (pinned) {
+		AOF_CUDA(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, st));
+		return AOF_OK;
+	}
+	const size_t chunk = 4u << 20;
+	for (size_t o = 0; o < bytes; o += chunk) {
+		const size_t len = bytes - o < chunk ? bytes - o : chunk;
+		memcpy((char *)stage + o, (const char *)src + o, len);
+		AOF_CUDA(cudaMemcpyAsync((char *)d_dst + o, (char *)stage + o, len, cudaMemcpyHostToDevice, st));
+	}
+	return AOF_OK;
+}
+
 } // namespace aof
 
 using namespace aof;
@@ -201,13 +219,8 @@ int aof_px4_calc_flow_batch(aof_px4 *h, const uint8_t *imgs, const uint32_t *t_u
 	if (rc != AOF_OK) return rc;
 	const size_t total = h->frame_bytes * h->n;
 	uint8_t *d_cur = h->d_frames[h->slot];
-	// stage pageable -> pinned in chunks so the CPU copy of chunk k+1 overlaps the DMA of chunk k
-	const size_t chunk = 4u << 20;
-	for (size_t o = 0; o < total; o += chunk) {
-		const size_t len = total - o < chunk ? total - o : chunk;
-		memcpy(h->h_stage + o, imgs + o, len);
-		AOF_CUDA(cudaMemcpyAsync(d_cur + o, h->h_stage + o, len, cudaMemcpyHostToDevice, h->st));
-	}
+	rc = stage_h2d(d_cur, imgs, total, h->h_stage, h->st);
+	if (rc != AOF_OK) return rc;
 	memcpy(h->h_t, t_us, sizeof(uint32_t) * h->n);
 	AOF_CUDA(cudaMemcpyAsync(h->d_t, h->h_t, sizeof(uint32_t) * h->n, cudaMemcpyHostToDevice, h->st));
 	rc = aof_px4_calc_flow_device(h, d_cur, h->d_t, h->d_out, nullptr, nullptr, h->st);

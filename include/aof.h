@@ -125,6 +125,68 @@ int aof_px4_compute_flow_pairs_device(aof_px4 *h, const uint8_t *d_prev, const u
 /* forget previous frames and limiter state (as a freshly constructed object) */
 int aof_px4_reset(aof_px4 *h);
 
+/* ------------------------------------------------------------------- LK path */
+
+/* ctor arguments of OpticalFlowOpenCV (include/flow_opencv.hpp:81-83; defaults
+ * :53-54 and include/optical_flow.hpp:47-49). */
+typedef struct aof_lk_params {
+	float focal_length_x, focal_length_y; /* px */
+	int output_rate;                      /* Hz; <= 0: publish every frame */
+	int image_width, image_height;
+	int num_features;                     /* 1..100 (trackFeatures.cpp:56) */
+	float confidence_multiplier;          /* 1.645 */
+} aof_lk_params;
+
+void aof_lk_default_params(aof_lk_params *p);
+
+/* per-call diagnostics of one stream (the values flow_opencv.cpp:121-202 derives) */
+typedef struct aof_lk_raw {
+	float px_x, px_y;  /* mean pixel flow after the confidence gate */
+	int32_t inliers;   /* meancount after the gate */
+	int32_t active;    /* features with status 1 before the gate */
+	int32_t fast_bins; /* bins FAST ran on in initMorePoints */
+	int32_t quality;   /* round(255 * inliers / N) before limitRate */
+} aof_lk_raw;
+
+typedef struct aof_lk aof_lk;
+
+/* replaces OpticalFlowOpenCV::OpticalFlowOpenCV (src/flow_opencv.cpp:47-65) for
+ * n_streams independent instances on CUDA device `device`.  The tracker state
+ * that the reference keeps in file statics (trackFeatures.cpp:53-56) is per stream. */
+int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **out);
+void aof_lk_destroy(aof_lk *h);
+int aof_lk_num_streams(const aof_lk *h);
+int aof_lk_reset(aof_lk *h);
+
+/* replaces OpticalFlowOpenCV::calcFlow (src/flow_opencv.cpp:89-210), 1-stream
+ * handle, synchronous.  Always writes flow_x/flow_y; dt_us only when it
+ * publishes (return >= 0) or output_rate <= 0. */
+int aof_lk_calc_flow(aof_lk *h, const uint8_t *img, uint32_t img_time_us, int *dt_us, float *flow_x, float *flow_y);
+
+/* all n_streams at once from HOST frames (back to back); out[n_streams]; raw may be NULL */
+int aof_lk_calc_flow_batch(aof_lk *h, const uint8_t *imgs, const uint32_t *t_us, aof_flow_out *out, aof_lk_raw *raw);
+
+/* device-resident form, asynchronous on cuda_stream.  d_imgs must stay valid
+ * and unchanged until the NEXT call has completed (it is level 0 of the previous
+ * pyramid; no copy is made).  d_raw may be NULL. */
+int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
+			    aof_lk_raw *d_raw, void *cuda_stream);
+
+/* state read-back for tests: per stream N entries of updateVector, features_current
+ * (x, y), prev_corners (x, y) and prev_status.  Any pointer may be NULL. */
+int aof_lk_get_state(aof_lk *h, int32_t *update_vec, float *feat_cur, float *prev_corners, uint8_t *prev_status);
+
+/* kernel-level entry points (known-answer tests; all HOST pointers, synchronous) */
+/* levels of cv::buildOpticalFlowPyramid for n frames: returns the number of levels L,
+ * writes level sizes to lw[4]/lh[4] and, if levels != NULL, the levels of frame i
+ * back to back at levels + i * (sum of level sizes). */
+int aof_lk_pyramid(aof_lk *h, const uint8_t *imgs, int n, int *lw, int *lh, uint8_t *levels);
+/* cv::calcOpticalFlowPyrLK(prev, cur, pts, Size(9,9), 3) for n frame pairs with n_pts points each */
+int aof_lk_track_points(aof_lk *h, const uint8_t *prev, const uint8_t *cur, int n, const float *pts, int n_pts,
+			float *next_pts, uint8_t *status);
+/* cv::FAST(bin ROI, 10, nonmax) on all 16 bins of n frames: score[n * w * h], 0 = no keypoint */
+int aof_lk_fast_scores(aof_lk *h, const uint8_t *imgs, int n, uint8_t *score);
+
 /* number of kernel launches this library has issued in this process */
 uint64_t aof_launch_count(void);
 
