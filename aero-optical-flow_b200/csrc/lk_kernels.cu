@@ -348,18 +348,22 @@ __device__ __forceinline__ int fast_score(const uint8_t *p, int pitch, int thr)
 #pragma unroll
 	for (int k = 0; k < 16; k++) { mp |= (unsigned)(d[k] > thr) << k; mn |= (unsigned)(d[k] < -thr) << k; }
 	if (!has_arc9(mp) && !has_arc9(mn)) return 0;
-	// exact response: max over the 16 arcs of max(min d, -max d), minus 1
-	int lo2[16], hi2[16], lo4[16], hi4[16];
+	// exact response: max over the 16 arcs of max(min d, min e), e = -d, minus 1.
+	// (e is materialised: ptxas 12.9 drops the negation when it folds max(m, -hi9) into VIMNMX3 on sm_100a.)
+	int e[16];
 #pragma unroll
-	for (int k = 0; k < 16; k++) { lo2[k] = min(d[k], d[(k + 1) & 15]); hi2[k] = max(d[k], d[(k + 1) & 15]); }
+	for (int k = 0; k < 16; k++) e[k] = -d[k];
+	int d2[16], e2[16], d4[16], e4[16];
 #pragma unroll
-	for (int k = 0; k < 16; k++) { lo4[k] = min(lo2[k], lo2[(k + 2) & 15]); hi4[k] = max(hi2[k], hi2[(k + 2) & 15]); }
+	for (int k = 0; k < 16; k++) { d2[k] = min(d[k], d[(k + 1) & 15]); e2[k] = min(e[k], e[(k + 1) & 15]); }
+#pragma unroll
+	for (int k = 0; k < 16; k++) { d4[k] = min(d2[k], d2[(k + 2) & 15]); e4[k] = min(e2[k], e2[(k + 2) & 15]); }
 	int m = -1000;
 #pragma unroll
 	for (int k = 0; k < 16; k++) {
-		const int lo9 = min(min(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
-		const int hi9 = max(max(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
-		m = max(m, max(lo9, -hi9));
+		const int d9 = min(min(d4[k], d4[(k + 4) & 15]), d[(k + 8) & 15]);
+		const int e9 = min(min(e4[k], e4[(k + 4) & 15]), e[(k + 8) & 15]);
+		m = max(m, max(d9, e9));
 	}
 	return m - 1;
 }
