@@ -59,6 +59,10 @@ def lib():
     L.aof_last_error.restype = C.c_char_p
     L.aof_device_count.restype = C.c_int
     L.aof_launch_count.restype = C.c_uint64
+    L.aof_timing_enable.argtypes = [C.c_int]
+    L.aof_timing_enable.restype = None
+    L.aof_timing_reset.restype = None
+    L.aof_timing_read.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     L.aof_px4_default_params.argtypes = [C.POINTER(Px4Params)]
     L.aof_px4_create.argtypes = [C.POINTER(Px4Params), C.c_int, C.c_int, C.POINTER(vp)]
     L.aof_px4_destroy.argtypes = [vp]
@@ -80,11 +84,25 @@ def lib():
     L.aof_lk_calc_flow_batch.argtypes = [vp, u8p, u32p, vp, vp]
     L.aof_lk_calc_flow_device.argtypes = [vp, u8p, u32p, vp, vp, vp]
     L.aof_lk_get_state.argtypes = [vp, vp, vp, vp, vp]
+    L.aof_lk_set_camera_matrix.argtypes = [vp] + [C.c_float] * 4
+    L.aof_lk_set_camera_distortion.argtypes = [vp] + [C.c_float] * 5
     L.aof_lk_pyramid.argtypes = [vp, u8p, C.c_int, vp, vp, vp]
     L.aof_lk_track_points.argtypes = [vp, u8p, u8p, C.c_int, vp, C.c_int, vp, vp]
     L.aof_lk_fast_scores.argtypes = [vp, u8p, C.c_int, vp]
     _lib = L
     return L
+
+
+def kernel_times():
+    """{kernel name: (total ms, launches)} recorded since aof_timing_reset (needs aof_timing_enable(1))."""
+    L = lib()
+    out = {}
+    for k in range(L.aof_timing_kernels()):
+        name = C.c_char_p(); ms = C.c_double(); cnt = C.c_uint64()
+        L.aof_timing_read(k, C.byref(name), C.byref(ms), C.byref(cnt))
+        if cnt.value:
+            out[name.value.decode()] = (ms.value, cnt.value)
+    return out
 
 
 def check(rc, what=""):
@@ -192,6 +210,12 @@ class LkFlow:
         check(lib().aof_lk_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), _ptr(out),
                                            _ptr(raw) if want_raw else None), "aof_lk_calc_flow_batch")
         return (out, raw) if want_raw else out
+
+    def set_camera_matrix(self, fx, fy, cx, cy):
+        check(lib().aof_lk_set_camera_matrix(self.handle, fx, fy, cx, cy), "aof_lk_set_camera_matrix")
+
+    def set_camera_distortion(self, k1, k2, k3, p1=0.0, p2=0.0):
+        check(lib().aof_lk_set_camera_distortion(self.handle, k1, k2, k3, p1, p2), "aof_lk_set_camera_distortion")
 
     def calc_flow_device(self, d_imgs, d_t_us, d_out, d_raw=0, stream=0):
         check(lib().aof_lk_calc_flow_device(self.handle, d_imgs, d_t_us, d_out, d_raw or None, stream or None),

@@ -60,6 +60,24 @@ AOF_HD int limit_rate(LimiterState &l, int output_rate, int quality, uint32_t t_
 
 void count_launch(uint64_t n = 1);
 
+// kernel ids of the optional per-kernel event timing (aof_timing_* in include/aof.h)
+enum KernelId {
+	KID_SAD_FLOW = 0, KID_PX4_EPILOGUE, KID_LK_PYR_DOWN, KID_LK_TRACK_UPDATE, KID_LK_FAST, KID_LK_SELECT_EPILOGUE,
+	KID_LK_TRACK_POINTS, KID_SAD_DENSE, KID_GFTT_MIN_EIG, KID_GFTT_SELECT, KID_LK_PYR_FUSED, KID_COUNT
+};
+
+// brackets one launch with two events when timing is enabled; a no-op otherwise
+class KernelTimer {
+public:
+	KernelTimer(int kid, cudaStream_t st);
+	~KernelTimer();
+private:
+	int kid_;
+	cudaStream_t st_;
+	void *a_ = nullptr, *b_ = nullptr;
+	bool active_ = false;
+};
+
 cudaError_t sad_flow_launch(int search, const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n,
 			    aof_px4_raw *raw, aof_px4_block *blocks, cudaStream_t st);
 cudaError_t px4_epilogue_launch(const aof_px4_raw *raw, const uint32_t *t_us, LimiterState *lim, aof_flow_out *out,
@@ -107,6 +125,13 @@ struct LkState {
 	uint32_t *kp;           // [n * 16 * kp_cap]  score << 24 | bin-local raster index
 };
 
+// camera model of setCameraMatrix / setCameraDistortion (flow_opencv.cpp:72-87); on only when both were set
+struct LkCamera {
+	int on;
+	float fx, fy, cx, cy;
+	float k1, k2, p1, p2, k3;
+};
+
 cudaError_t lk_pyr_down_launch(const uint8_t *src, uint8_t *dst, int sw, int sh, int n, cudaStream_t st);
 cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
 				   int have_prev, cudaStream_t st);
@@ -114,7 +139,7 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 			   cudaStream_t st);
 cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
 				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
-				      float fy, cudaStream_t st);
+				      float fy, const LkCamera &cam, cudaStream_t st);
 // stateless pyramidal LK over given points (KAT entry): pts[n * n_pts]
 cudaError_t lk_track_points_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const float2 *pts, int n_pts,
 				   float2 *out, uint8_t *status, int n, cudaStream_t st);

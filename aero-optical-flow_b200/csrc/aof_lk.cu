@@ -25,6 +25,8 @@ struct aof_lk {
 	const uint8_t *l0[2] = {nullptr, nullptr};
 	int cur = 0;
 	bool have_prev = false, have_feat_prev = false;
+	bool set_cam = false, set_dist = false;
+	LkCamera cam{};
 	LkState s{};
 	// host-batch path (allocated on first use)
 	uint8_t *d_frames[2] = {nullptr, nullptr};
@@ -189,7 +191,7 @@ int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_
 	AOF_CUDA(lk_fast_launch(h->g, d_imgs, h->s, h->n, nullptr, st));
 	AOF_CUDA(lk_select_epilogue_launch(h->g, h->s, d_t_us, d_out, d_raw, h->n, h->have_feat_prev ? 1 : 0,
 					   h->p.output_rate, h->p.confidence_multiplier, h->p.focal_length_x,
-					   h->p.focal_length_y, st));
+					   h->p.focal_length_y, h->cam, st));
 	h->cur = nxt;
 	h->have_prev = h->have_feat_prev = true;
 	return AOF_OK;
@@ -244,6 +246,26 @@ int aof_lk_calc_flow(aof_lk *h, const uint8_t *img, uint32_t img_time_us, int *d
 	*flow_y = o.flow_y;
 	if (o.quality >= 0 || h->p.output_rate <= 0) *dt_us = o.dt_us;
 	return o.quality;
+}
+
+/* OpticalFlowOpenCV::setCameraMatrix (src/flow_opencv.cpp:72-80) */
+int aof_lk_set_camera_matrix(aof_lk *h, float focal_len_x, float focal_len_y, float principal_point_x, float principal_point_y)
+{
+	if (!h) return AOF_ERR_INVALID;
+	h->cam.fx = focal_len_x; h->cam.fy = focal_len_y; h->cam.cx = principal_point_x; h->cam.cy = principal_point_y;
+	h->set_cam = true;
+	h->cam.on = h->set_cam && h->set_dist;
+	return AOF_OK;
+}
+
+/* OpticalFlowOpenCV::setCameraDistortion(k1, k2, k3, p1, p2) (src/flow_opencv.cpp:82-87) */
+int aof_lk_set_camera_distortion(aof_lk *h, float k1, float k2, float k3, float p1, float p2)
+{
+	if (!h) return AOF_ERR_INVALID;
+	h->cam.k1 = k1; h->cam.k2 = k2; h->cam.k3 = k3; h->cam.p1 = p1; h->cam.p2 = p2;
+	h->set_dist = true;
+	h->cam.on = h->set_cam && h->set_dist;
+	return AOF_OK;
 }
 
 int aof_lk_get_state(aof_lk *h, int32_t *update_vec, float *feat_cur, float *prev_corners, uint8_t *prev_status)

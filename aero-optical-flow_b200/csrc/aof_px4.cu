@@ -1,59 +1,12 @@
 // C-ABI host side of the SAD path (include/aof.h): per-stream device state,
 // pinned staging, async copies, launches.  Replaces the host logic of
 // OpticalFlowPX4 (src/flow_px4.cpp:47-98); the arithmetic is in sad_kernels.cu.
-#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <new>
 
 #include "aof_internal.h"
 #include "aof_host.h"
-
-namespace aof {
-
-static std::atomic<uint64_t> g_launches{0};
-void count_launch(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
-
-static thread_local char g_err[512] = "";
-void set_error(const char *fmt, ...)
-{
-	va_list ap;
-	va_start(ap, fmt);
-	vsnprintf(g_err, sizeof g_err, fmt, ap);
-	va_end(ap);
-}
-const char *last_error() { return g_err; }
-
-int select_device(int device)
-{
-	int n = 0;
-	cudaError_t e = cudaGetDeviceCount(&n);
-	if (e != cudaSuccess) { set_error("cudaGetDeviceCount: %s", cudaGetErrorString(e)); return AOF_ERR_CUDA; }
-	if (n == 0) { set_error("no CUDA device (this library has no CPU fallback)"); return AOF_ERR_NO_DEVICE; }
-	if (device < 0 || device >= n) { set_error("device %d out of range (%d present)", device, n); return AOF_ERR_INVALID; }
-	AOF_CUDA(cudaSetDevice(device));
-	return AOF_OK;
-}
-
-int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStream_t st)
-{
-	cudaPointerAttributes at{};
-	const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
-	cudaGetLastError();
-	if (pinned) {
-		AOF_CUDA(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, st));
-		return AOF_OK;
-	}
-	const size_t chunk = 4u << 20;
-	for (size_t o = 0; o < bytes; o += chunk) {
-		const size_t len = bytes - o < chunk ? bytes - o : chunk;
-		memcpy((char *)stage + o, (const char *)src + o, len);
-		AOF_CUDA(cudaMemcpyAsync((char *)d_dst + o, (char *)stage + o, len, cudaMemcpyHostToDevice, st));
-	}
-	return AOF_OK;
-}
-
-} // namespace aof
 
 using namespace aof;
 
@@ -84,16 +37,7 @@ struct aof_px4 {
 
 extern "C" {
 
-const char *aof_version(void) { return "aof_b200 0.1 (sm_100a)"; }
-const char *aof_last_error(void) { return last_error(); }
-uint64_t aof_launch_count(void) { return g_launches.load(); }
 
-int aof_device_count(void)
-{
-	int n = 0;
-	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
-	return n;
-}
 
 void aof_px4_default_params(aof_px4_params *p)
 {

@@ -66,6 +66,7 @@ cudaError_t lk_pyr_down_launch(const uint8_t *src, uint8_t *dst, int sw, int sh,
 	if (n <= 0) return cudaSuccess;
 	const int dw = (sw + 1) / 2, dh = (sh + 1) / 2;
 	dim3 grid((dw + PD_TW - 1) / PD_TW, (dh + PD_TH - 1) / PD_TH, n);
+	KernelTimer kt(KID_LK_PYR_DOWN, st);
 	lk_pyr_down_kernel<<<grid, 256, 0, st>>>(src, dst, sw, sh, dw, dh);
 	count_launch();
 	return cudaGetLastError();
@@ -292,6 +293,7 @@ cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkP
 				   int have_prev, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
+	KernelTimer kt(KID_LK_TRACK_UPDATE, st);
 	lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
 	count_launch();
 	return cudaGetLastError();
@@ -318,6 +320,7 @@ cudaError_t lk_track_points_launch(const LkGeom &g, const LkPyr &prev, const LkP
 {
 	const long long total = (long long)n * n_pts;
 	if (total <= 0) return cudaSuccess;
+	KernelTimer kt(KID_LK_TRACK_POINTS, st);
 	lk_track_points_kernel<<<(unsigned)((total + 7) / 8), 256, 0, st>>>(g, prev, next, pts, n_pts, out, status, n);
 	count_launch();
 	return cudaGetLastError();
@@ -421,6 +424,7 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 	if (n <= 0) return cudaSuccess;
 	const int tiles_x = (g.bw + FT_TW - 1) / FT_TW, tiles_y = (g.bh + FT_TH - 1) / FT_TH;
 	dim3 grid(tiles_x * tiles_y * LK_BINS, n);
+	KernelTimer kt(KID_LK_FAST, st);
 	lk_fast_kernel<<<grid, 256, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
 	count_launch();
 	return cudaGetLastError();
@@ -445,10 +449,31 @@ __device__ __forceinline__ bool cheb_close(int ax, int ay, int bx, int by, int d
 	return abs(ax - bx) < dist && abs(ay - by) < dist;
 }
 
+// cv::undistortPoints(src, dst, K, D) -- 5 fixed-point iterations in double, no R / P -- followed by the
+// re-projection of flow_opencv.cpp:113-118 in float
+__device__ float2 lk_undistort(const LkCamera &c, float2 pt)
+{
+	const double fx = c.fx, fy = c.fy, cx = c.cx, cy = c.cy;
+	const double k1 = c.k1, k2 = c.k2, p1 = c.p1, p2 = c.p2, k3 = c.k3;
+	const double ifx = 1. / fx, ify = 1. / fy;
+	const double u = pt.x, v = pt.y;
+	double x = (u - cx) * ifx, y = (v - cy) * ify;
+	const double x0 = x, y0 = y;
+	for (int j = 0; j < 5; j++) {
+		const double r2 = x * x + y * y;
+		const double icdist = 1. / (1 + ((k3 * r2 + k2) * r2 + k1) * r2);
+		if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+		const double dx = 2 * p1 * x * y + p2 * (r2 + 2 * x * x);
+		const double dy = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y;
+		x = (x0 - dx) * icdist; y = (y0 - dy) * icdist;
+	}
+	return make_float2((float)x * c.fx + c.cx, (float)y * c.fy + c.cy);
+}
+
 __global__ void __launch_bounds__(SEL_THREADS)
 lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us, aof_flow_out *__restrict__ out,
 			  aof_lk_raw *__restrict__ raw, int have_feat_prev, int output_rate, float conf, float focal_x,
-			  float focal_y)
+			  float focal_y, LkCamera cam)
 {
 	__shared__ int s_ex[LK_MAX_FEATURES], s_ey[LK_MAX_FEATURES];
 	__shared__ int s_nex, s_ngood, s_done;
@@ -597,6 +622,10 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 		}
 	}
 
+	// ---- optional undistortion of every slot, placeholders included (flow_opencv.cpp:108-119)
+	if (cam.on)
+		for (int i = 0; i < N; i++) fc[i] = lk_undistort(cam, fc[i]);
+
 	// ---- calcFlow statistics (flow_opencv.cpp:121-180)
 	int meancount = 0, active = 0;
 	float mx = 0.f, my = 0.f;
@@ -651,10 +680,11 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 
 cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
 				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
-				      float fy, cudaStream_t st)
+				      float fy, const LkCamera &cam, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
-	lk_select_epilogue_kernel<<<n, SEL_THREADS, 0, st>>>(g, s, t_us, out, raw, have_feat_prev, output_rate, conf, fx, fy);
+	KernelTimer kt(KID_LK_SELECT_EPILOGUE, st);
+	lk_select_epilogue_kernel<<<n, SEL_THREADS, 0, st>>>(g, s, t_us, out, raw, have_feat_prev, output_rate, conf, fx, fy, cam);
 	count_launch();
 	return cudaGetLastError();
 }

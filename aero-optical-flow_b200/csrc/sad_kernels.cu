@@ -277,6 +277,7 @@ template <int S> static cudaError_t launch_sad(const uint8_t *prev, const uint8_
 		if (e != cudaSuccess) return e;
 		attr_set[dev] = true;
 	}
+	KernelTimer kt(KID_SAD_FLOW, st);
 	sad_flow_kernel<S><<<n, SadCfg<S>::THREADS, dyn, st>>>(prev, cur, g, raw, blocks);
 	count_launch();
 	return cudaGetLastError();
@@ -298,6 +299,7 @@ cudaError_t px4_epilogue_launch(const aof_px4_raw *raw, const uint32_t *t_us, Li
 				int n, int output_rate, float fx, float fy, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
+	KernelTimer kt(KID_PX4_EPILOGUE, st);
 	px4_epilogue_kernel<<<(n + 127) / 128, 128, 0, st>>>(raw, t_us, lim, out, n, output_rate, fx, fy);
 	count_launch();
 	return cudaGetLastError();

@@ -1,12 +1,17 @@
 #!/usr/bin/env python
 """bench.py -- frame-pairs/s of the calcFlow hot path on N B200s (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload sad|lk] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload lk|sad|both] [--impl reference]
 
-One process per GPU (torchrun for N>1).  A "step" is one calcFlow pass over one batch
-of independent streams (SAD: 4096 streams of 64x64, search +-4 = BASELINE config 3),
-each rank owning whole streams (weak scaling, no data-path collective; torch.distributed
-is used only for the barrier and the max-over-ranks of the device time).
+One process per GPU (torchrun for N>1).  A "step" is one calcFlow pass over one batch of
+independent streams, each rank owning whole streams (weak scaling, no data-path collective;
+torch.distributed is used only for the barrier and the max-over-ranks of the device time).
+
+  lk  (primary, BASELINE configs[1] batched as in configs[4]): OpticalFlowOpenCV::calcFlow on
+      640x480 frames, 20 features, 512 streams per GPU per launch.
+  sad (BASELINE configs[2]): OpticalFlowPX4::calcFlow on 64x64 frames, search +-4, 4096 streams
+      per GPU per launch.  With --workload both (default) it is reported inside the same JSON
+      line under "sad".
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -23,13 +28,15 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 import __graft_entry__ as entry  # noqa: E402
 
-SAD_STREAMS = 4096
-SAD_W = SAD_H = 64
-SAD_SEARCH = 4
-SAD_ROT = 16                      # distinct frame buffers the current frame rotates over (16 x 16 MiB > L2)
-SAD_BYTES_PER_PAIR = 2 * SAD_W * SAD_H + 16   # both frames read + 16 B result
-SAD_INSTR_PER_PAIR = 40550        # packed-byte instructions of the reference algorithm
 FX, FY = 216.6677, 216.2457
+# ---- SAD workload
+SAD_STREAMS, SAD_W, SAD_H, SAD_SEARCH, SAD_ROT = 4096, 64, 64, 4, 16
+SAD_BYTES_PER_PAIR = 2 * SAD_W * SAD_H + 16      # both frames read + 16 B result
+SAD_INSTR_PER_PAIR = 40550                       # packed-byte instructions of the reference algorithm
+# ---- LK workload (SURVEY.md 8(d), config 2 batched)
+LK_STREAMS, LK_W, LK_H, LK_FEATURES, LK_ROT = 512, 640, 480, 20, 4
+LK_LEVEL_PX = [640 * 480, 320 * 240, 160 * 120, 80 * 60]
+LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read once + L1..L3 written = 408 000 B
 
 
 def peaks():
@@ -94,18 +101,17 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def dist_setup(n_gpus):
+def dist_setup():
     import torch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    else:
-        torch.cuda.set_device(local)
+        if not dist.is_initialized():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     return rank, world, local
 
 
@@ -127,9 +133,24 @@ def max_over_ranks(ms, world):
     return float(t.item())
 
 
-# ----------------------------------------------------------------------------- CPU arms
+def time_steps(step, first, steps, world):
+    """`steps` calls of step(k) between a barrier + sync on both sides; device time, max over ranks (ms)."""
+    import torch
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(steps):
+        step(first + k)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    barrier(world)
+    return ms
+
+
+# ----------------------------------------------------------------------------- synthetic inputs
 def sad_host_frames(n, rot, seed):
-    """rot consecutive frames of n translating streams (numpy, host)."""
+    """rot consecutive frames of n translating 64x64 streams (numpy, host)."""
     pkg = entry.load_package()
     rng = np.random.default_rng(seed)
     span = SAD_SEARCH * (rot // 2) + 8
@@ -144,8 +165,32 @@ def sad_host_frames(n, rot, seed):
     return frames, vel
 
 
+def lk_host_frames(n, rot, seed, out=None):
+    """rot frames of n translating 640x480 streams: 8 Gaussian-blurred noise textures (sigma 2, as
+    SURVEY.md 8(d)), each stream a different window and velocity; triangle-wave positions so that
+    every consecutive pair, and the wrap-around, is a pure translation by +-vel."""
+    from scipy.ndimage import gaussian_filter
+    rng = np.random.default_rng(seed)
+    n_tex, m = 8, 64
+    tex = []
+    for t in range(n_tex):
+        a = gaussian_filter(rng.random((LK_H + 2 * m + 64, LK_W + 2 * m + 64)), 2.0, mode="wrap")
+        a -= a.min(); a /= a.max()
+        tex.append(np.round(a * 255.0).astype(np.uint8))
+    vel = rng.integers(-5, 6, (n, 2))
+    org = rng.integers(0, 64, (n, 2))
+    frames = out if out is not None else np.empty((rot, n, LK_H, LK_W), np.uint8)
+    for k in range(rot):
+        p = k if k <= rot // 2 else rot - k
+        for i in range(n):
+            ox, oy = m + org[i, 0] - p * vel[i, 0], m + org[i, 1] - p * vel[i, 1]
+            frames[k, i] = tex[i % n_tex][oy:oy + LK_H, ox:ox + LK_W]
+    return frames, vel
+
+
+# ----------------------------------------------------------------------------- CPU arms
 def cpu_sad_runner():
-    """-> (fn(prev, cur, threads) -> seconds, kind)"""
+    """-> (fn(prev, cur, threads), kind): the unmodified reference objects when oracle/_ref was built"""
     from oracle import sad as osad
     if osad.ref_available():
         R = osad.Ref()
@@ -154,7 +199,7 @@ def cpu_sad_runner():
     return (lambda p, c, th: P.compute_flow_batch(p, c, SAD_SEARCH, 30, 3000)), "port"
 
 
-def cpu_baseline_sad(frames, budget_s=12.0):
+def cpu_sad(frames, budget_s):
     fn, kind = cpu_sad_runner()
     cores = os.cpu_count() or 1
     threads = cores if kind == "reference" else 1
@@ -167,52 +212,104 @@ def cpu_baseline_sad(frames, budget_s=12.0):
         fn(frames[r % (len(frames) - 1)], frames[r % (len(frames) - 1) + 1], threads)
     dt = time.perf_counter() - t0
     return {"value": reps * n / dt, "unit": "frame-pairs/s", "cores": threads, "kind": kind,
-            "sample": "%d x %d SAD 64x64 +-%d pairs, PX4Flow::compute_flow, %d host threads" % (reps, n, SAD_SEARCH, threads)}
+            "sample": "%d x %d SAD 64x64 +-%d pairs, PX4Flow::compute_flow (%s), %d host threads" % (reps, n, SAD_SEARCH, kind, threads)}
+
+
+def cpu_lk(frames, budget_s):
+    """oracle/lk_oracle.c trackers (flow_opencv.cpp cannot be compiled here: kind 'port'), one per stream,
+    spread over all host cores with threads (ctypes releases the GIL inside the C call)."""
+    from oracle import lk as olk
+    cores = os.cpu_count() or 1
+    rot, n = frames.shape[:2]
+    tr = olk.Tracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES)
+    tr.calc_flow(frames[0, 0], 0)
+    t0 = time.perf_counter(); tr.calc_flow(frames[1, 0], 1000); per_pair = time.perf_counter() - t0
+    n_frames = 4                                             # calls per stream after the priming frame
+    streams = int(max(cores, min(n, budget_s * cores / (per_pair * n_frames))))
+    trackers = [olk.Tracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES) for _ in range(streams)]
+    for i, t in enumerate(trackers):
+        t.calc_flow(frames[0, i % n], 0)                     # priming frame (detection only), untimed
+
+    def work(tid):
+        for i in range(tid, streams, cores):
+            for k in range(1, n_frames + 1):
+                trackers[i].calc_flow(frames[k % rot, i % n], 1000 * k)
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    return {"value": streams * n_frames / dt, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
+            "sample": "%d streams x %d frames, LK 640x480, 20 features, oracle/lk_oracle.c (CPU restatement of "
+                      "flow_opencv.cpp + trackFeatures.cpp + the OpenCV arithmetic), %d host threads" % (streams, n_frames, cores)}
 
 
 def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    frames, _ = sad_host_frames(SAD_STREAMS, 3, 1)
-    fn, kind = cpu_sad_runner()
-    cores = os.cpu_count() or 1
-    threads = cores if kind == "reference" else 1
-    t0 = time.perf_counter(); fn(frames[0][:512], frames[1][:512], threads); per_pair = (time.perf_counter() - t0) / 512
+    entry.build_oracles()
+    budget = 60.0
+    if args.workload == "sad":
+        frames, _ = sad_host_frames(SAD_STREAMS, 3, 1)
+        workload, fn = "sad64_batch4096_search4", cpu_sad
+    else:
+        frames, _ = lk_host_frames(64, LK_ROT, 1)
+        workload, fn = "lk640x480_features20", cpu_lk
     total = max(1, args.steps + args.warmup)
-    sample = int(min(SAD_STREAMS, max(32, 90.0 / total / per_pair)))
-    for w in range(args.warmup):
-        fn(frames[w % 2][:sample], frames[w % 2 + 1][:sample], threads)
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        fn(frames[k % 2][:sample], frames[k % 2 + 1][:sample], threads)
-    dt = time.perf_counter() - t0
-    v = args.steps * sample / dt
-    desc = "%d of %d streams per step, SAD 64x64 +-%d, %s CPU code, %d host threads" % (sample, SAD_STREAMS, SAD_SEARCH, kind, threads)
+    vals = []
+    for k in range(total):
+        r = fn(frames, budget / total)
+        if k >= args.warmup:
+            vals.append(r)
+    v = float(np.mean([r["value"] for r in vals]))
+    ms = 1e3 * float(np.mean([1.0 / r["value"] for r in vals]))
+    cb = dict(vals[-1]); cb["value"] = v
     print(json.dumps({
         "impl": "reference", "metric": "frame-pairs/s", "value": v, "unit": "frame-pairs/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / max(1, args.steps) * 1e3, "higher_is_better": True,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "sad64_batch4096_search4", "streams_per_gpu": SAD_STREAMS, "sample_per_step": sample},
-        "cpu_baseline": {"value": v, "unit": "frame-pairs/s", "cores": threads, "kind": kind, "sample": desc},
-        "e2e": {"value": v, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": {"workload": workload, "note": "each step is a bounded sample of the workload on the host cores; ms_per_step is per frame pair"},
+        "cpu_baseline": cb, "e2e": {"value": v, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 
-# ----------------------------------------------------------------------------- GPU arm (SAD)
-def run_sad(args):
+# ----------------------------------------------------------------------------- GPU arms
+def kernel_breakdown(pkg, step, first, steps):
+    """per-kernel device time of `steps` steps through the library's own event timing"""
+    import torch
+    L = pkg.lib()
+    L.aof_timing_reset(); L.aof_timing_enable(1)
+    for k in range(steps):
+        step(first + k)
+    torch.cuda.synchronize()
+    times = pkg.capi.kernel_times()
+    L.aof_timing_enable(0)
+    return {name: {"ms_per_step": ms / steps, "launches_per_step": cnt / steps} for name, (ms, cnt) in times.items()}
+
+
+def pinned_frames(shape):
+    import torch
+    t = torch.empty(shape, dtype=torch.uint8, pin_memory=True)
+    return t, t.numpy()
+
+
+def run_sad_gpu(args, rank, world, local, with_cpu):
     import torch
     pkg = entry.load_package()
     L = pkg.lib()
-    rank, world, local = dist_setup(args.gpus)
     n, rot = SAD_STREAMS, SAD_ROT
     frames, vel = sad_host_frames(n, rot, seed=1000 + rank)
+    keep, h_frames = pinned_frames(frames.shape)
+    h_frames[:] = frames
     fb = n * SAD_W * SAD_H
     d_frames = torch.empty((rot, fb), dtype=torch.uint8, device="cuda")
-    d_frames.copy_(torch.from_numpy(frames.reshape(rot, fb)))
+    d_frames.copy_(keep.reshape(rot, fb))
     d_t = torch.zeros((rot, n), dtype=torch.int32, device="cuda")
     d_out = torch.zeros((n, 4), dtype=torch.int32, device="cuda")
-    d_raw = torch.zeros((n, 4), dtype=torch.int32, device="cuda")
     flow = pkg.Px4Flow(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=n, device=local)
     stream = torch.cuda.current_stream().cuda_stream
     fptr = [d_frames[k].data_ptr() for k in range(rot)]
@@ -221,73 +318,47 @@ def run_sad(args):
     def step(k):
         flow.calc_flow_device(fptr[k % rot], tptr[k % rot], d_out.data_ptr(), stream=stream)
 
-    launches0 = L.aof_launch_count()
     for k in range(args.warmup + 1):          # +1: the priming frame launches nothing
         step(k)
-    barrier(world)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l_before = L.aof_launch_count()
-    e0.record()
-    for k in range(args.steps):
-        step(args.warmup + 1 + k)
-    e1.record()
-    torch.cuda.synchronize()
-    l_timed = L.aof_launch_count() - l_before
-    ms = max_over_ranks(e0.elapsed_time(e1), world)
-    barrier(world)
-    # keep the same loop running until the clock sampler has seen >= 1.5 s of it
-    t_end = time.time() + max(0.0, 1.5 - ms * 1e-3)
+    l0 = L.aof_launch_count()
+    ms = time_steps(step, args.warmup + 1, args.steps, world)
+    launches = L.aof_launch_count() - l0
+    t_end = time.time() + max(0.0, 1.5 - ms * 1e-3)   # keep the same loop running until the sampler has >= 1.5 s of it
     k = 0
     while time.time() < t_end:
         for _ in range(200):
             step(k); k += 1
         torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
-
-    # dominant kernel alone (sad_flow_kernel<4>, same launches as in the step): events around K launches
-    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    for k in range(5):
-        flow.compute_flow_pairs_device(fptr[k % rot], fptr[(k + 1) % rot], n, d_raw.data_ptr(), stream=stream)
-    torch.cuda.synchronize()
-    e2.record()
-    for k in range(args.steps):
-        flow.compute_flow_pairs_device(fptr[k % rot], fptr[(k + 1) % rot], n, d_raw.data_ptr(), stream=stream)
-    e3.record()
-    torch.cuda.synchronize()
-    kern_ms = e2.elapsed_time(e3) / args.steps
-
-    # parity spot check of the timed path (one stream against its known translation)
     out = d_out.cpu().numpy().view(pkg.capi.flow_out_dtype).reshape(-1)
-    assert (out["quality"] == 255).mean() > 0.99, "timed path produced implausible quality"
+    assert (out["quality"] == 255).mean() > 0.99, "timed SAD path produced implausible quality"
+    kb = kernel_breakdown(pkg, step, k, min(args.steps, 200))
 
-    # end to end through the host API: pageable host frames -> pinned staging -> H2D -> kernels -> D2H
+    # end to end through the host API: pinned host frames -> H2D -> kernels -> 16 B/stream D2H
     flow_e = pkg.Px4Flow(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=n, device=local)
     t_us = np.zeros(n, np.uint32)
-    e_steps = max(3, min(args.steps, 60))
+    e_steps = max(3, min(args.steps, 200))
     for k in range(4):
-        flow_e.calc_flow_batch(frames[k % rot], t_us + 1000 * k)
+        flow_e.calc_flow_batch(h_frames[k % rot], t_us + 1000 * k)
     barrier(world)
     t0 = time.perf_counter()
     for k in range(e_steps):
-        res = flow_e.calc_flow_batch(frames[(k + 4) % rot], t_us + 1000 * (k + 4))
+        res = flow_e.calc_flow_batch(h_frames[(k + 4) % rot], t_us + 1000 * (k + 4))
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    e2e_ms = max_over_ranks(e2e_s * 1e3, world)
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
     assert (res["quality"] == 255).mean() > 0.99
-    flow_e.close()
-
+    flow_e.close(); flow.close()
     if rank != 0:
-        return
+        return None
     pk = peaks()
-    value = world * n * args.steps / (ms * 1e-3)
+    dom = max(kb, key=lambda kname: kb[kname]["ms_per_step"])
+    kern_ms = kb["sad_flow_kernel"]["ms_per_step"]
     achieved = n * SAD_BYTES_PER_PAIR / (kern_ms * 1e-3) / 1e9
-    line = {
-        "metric": "frame-pairs/s", "value": value, "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+    r = {
+        "value": world * n * args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
         "config": {"workload": "sad64_batch4096_search4 (BASELINE config 3: OpticalFlowPX4::calcFlow, 4096 streams/GPU/launch)",
                    "streams_per_gpu": n, "image": "64x64", "search": SAD_SEARCH, "output_rate": -1,
                    "l2": "current frames rotate over %d buffers = %d MiB > 126 MB L2; the previous frame is last step's "
@@ -295,38 +366,179 @@ def run_sad(args):
                    "parallelism": "streams sharded across ranks, host gather, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk["which"],
-                     "kernel": "sad_flow_kernel<4>", "kernel_ms": kern_ms,
+                     "kernel": "sad_flow_kernel<4>", "kernel_ms": kern_ms, "dominant_kernel_by_time": dom,
                      "algorithmic_bytes_per_launch": n * SAD_BYTES_PER_PAIR},
+        "kernels": kb,
         "e2e": {"value": world * n * e_steps / (e2e_ms * 1e-3), "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": 16 * n, "steps": e_steps,
-                "api": "aof_px4_calc_flow_batch (host frames -> pinned staging -> H2D -> kernels -> D2H)"},
-        "gpu_launches": int(l_timed), "clocks": clocks,
+                "api": "aof_px4_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)"},
+        "gpu_launches": int(launches), "clocks": clocks, "dtype": "u8",
     }
     if "alu_packed_instr_per_s" in pk:
         a = n * SAD_INSTR_PER_PAIR / (kern_ms * 1e-3)
-        line["roofline_int_alu"] = {"bound": "int-alu (VABSDIFF4 issue rate, the binding one)", "achieved": a,
-                                    "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
-                                    "frac": a / pk["alu_packed_instr_per_s"], "peak_source": pk["alu_which"],
-                                    "algorithmic_instr_per_pair": SAD_INSTR_PER_PAIR}
-    if world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline_sad(frames)
-    print(json.dumps(line))
+        r["roofline_int_alu"] = {"bound": "int-alu (VABSDIFF4 issue rate, the binding one)", "achieved": a,
+                                 "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
+                                 "frac": a / pk["alu_packed_instr_per_s"], "peak_source": pk["alu_which"],
+                                 "algorithmic_instr_per_pair": SAD_INSTR_PER_PAIR}
+    if with_cpu:
+        r["cpu_baseline"] = cpu_sad(frames, 10.0)
+    return r
+
+
+def run_lk_gpu(args, rank, world, local, with_cpu):
+    import torch
+    pkg = entry.load_package()
+    L = pkg.lib()
+    n, rot = args.lk_streams, LK_ROT
+    keep, h_frames = pinned_frames((rot, n, LK_H, LK_W))
+    _, vel = lk_host_frames(n, rot, seed=2000 + rank, out=h_frames)
+    fb = n * LK_W * LK_H
+    d_frames = torch.empty((rot, fb), dtype=torch.uint8, device="cuda")
+    d_frames.copy_(keep.reshape(rot, fb))
+    d_t = torch.zeros((rot, n), dtype=torch.int32, device="cuda")
+    d_out = torch.zeros((n, 4), dtype=torch.int32, device="cuda")
+    d_raw = torch.zeros((n, 6), dtype=torch.int32, device="cuda")
+    flow = pkg.LkFlow(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=n, device=local)
+    stream = torch.cuda.current_stream().cuda_stream
+    fptr = [d_frames[k].data_ptr() for k in range(rot)]
+    tptr = [d_t[k].data_ptr() for k in range(rot)]
+
+    def step(k):
+        flow.calc_flow_device(fptr[k % rot], tptr[k % rot], d_out.data_ptr(), d_raw.data_ptr(), stream=stream)
+
+    for k in range(args.warmup + 1):          # +1: the first frame only detects
+        step(k)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = L.aof_launch_count()
+    ms = time_steps(step, args.warmup + 1, args.steps, world)
+    launches = L.aof_launch_count() - l0
+    k = args.warmup + 1 + args.steps
+    t_end = time.time() + max(0.0, 1.5 - ms * 1e-3)
+    while time.time() < t_end:
+        for _ in range(20):
+            step(k); k += 1
+        torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+    # parity spot check of the timed path: the flow of a translating texture is its translation
+    raw = d_raw.cpu().numpy().view(pkg.capi.lk_raw_dtype).reshape(-1)
+    p = (k - 1) % rot
+    sign = 1.0 if 1 <= p <= rot // 2 else -1.0     # the last step went forward or back along the triangle wave
+    ok = (np.abs(raw["px_x"] - sign * vel[:, 0]) < 1e-2) & (np.abs(raw["px_y"] - sign * vel[:, 1]) < 1e-2) & (raw["inliers"] >= 5)
+    assert ok.mean() > 0.97, "timed LK path does not recover the translations (%.3f ok)" % ok.mean()
+    kb = kernel_breakdown(pkg, step, k, min(args.steps, 50))
+    k += min(args.steps, 50)
+
+    # end to end through the host API: pinned host frames -> H2D -> kernels -> 16 B/stream D2H
+    flow.close()
+    flow_e = pkg.LkFlow(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=n, device=local)
+    t_us = np.zeros(n, np.uint32)
+    e_steps = max(3, min(args.steps, 30))
+    for j in range(3):
+        flow_e.calc_flow_batch(h_frames[j % rot], t_us + 1000 * j)
+    barrier(world)
+    t0 = time.perf_counter()
+    for j in range(e_steps):
+        res = flow_e.calc_flow_batch(h_frames[(j + 3) % rot], t_us + 1000 * (j + 3))
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+    assert (res["quality"] > 60).mean() > 0.97
+    flow_e.close()
+
+    # single-stream latency (BASELINE config 2 as written: one stream, host frame in, result out)
+    one = pkg.LkFlow(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=1, device=local)
+    for j in range(4):
+        one.calc_flow(h_frames[j % rot, 0], 1000 * j)
+    t0 = time.perf_counter()
+    for j in range(40):
+        one.calc_flow(h_frames[(j + 4) % rot, 0], 1000 * (j + 4))
+    lat_us = (time.perf_counter() - t0) / 40 * 1e6
+    one.close()
+    if rank != 0:
+        return None
+    pk = peaks()
+    dom = max(kb, key=lambda kname: kb[kname]["ms_per_step"])
+    step_ms = ms / args.steps
+    # algorithmic bytes per launch of the dominant kernel
+    alg = {"lk_pyr_down_kernel": n * (LK_LEVEL_PX[0] + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0,
+           "lk_pyr_fused_kernel": n * LK_BYTES_PER_PAIR, "lk_fast_kernel": n * LK_LEVEL_PX[0]}
+    dom_bytes = alg.get(dom, n * LK_BYTES_PER_PAIR)
+    dom_ms = kb[dom]["ms_per_step"] / max(1.0, kb[dom]["launches_per_step"])
+    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+    r = {
+        "value": world * n * args.steps / (ms * 1e-3), "ms_per_step": step_ms,
+        "config": {"workload": "lk640x480_features20 (BASELINE config 2 batched: OpticalFlowOpenCV::calcFlow, %d streams/GPU/launch, "
+                               "FAST + binned selection + 3-level pyramidal LK 9x9)" % n,
+                   "streams_per_gpu": n, "image": "640x480", "features": LK_FEATURES, "output_rate": -1,
+                   "l2": "frames rotate over %d buffers = %d MiB > 126 MB L2" % (rot, rot * fb >> 20),
+                   "parallelism": "streams sharded across ranks, host gather, no collective"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                     "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk["which"],
+                     "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
+                     "step": {"algorithmic_bytes_per_step": n * LK_BYTES_PER_PAIR,
+                              "achieved": n * LK_BYTES_PER_PAIR / (step_ms * 1e-3) / 1e9,
+                              "frac": n * LK_BYTES_PER_PAIR / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"]}},
+        "kernels": kb,
+        "e2e": {"value": world * n * e_steps / (e2e_ms * 1e-3), "unit": "frame-pairs/s",
+                "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
+                "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)"},
+        "single_stream_latency_us": lat_us,
+        "gpu_launches": int(launches), "clocks": clocks, "dtype": "u8 (i32 / f32 in LK)",
+    }
+    if with_cpu:
+        r["cpu_baseline"] = cpu_lk(h_frames[:, :64], 12.0)
+    return r
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2000)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="sad", choices=["sad"])
+    ap.add_argument("--workload", default="both", choices=["lk", "sad", "both"])
+    ap.add_argument("--lk-streams", type=int, default=LK_STREAMS)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
+        if args.workload == "both":
+            args.workload = "lk"
         run_reference(args)
-    else:
-        run_sad(args)
+        return
+    rank, world, local = dist_setup()
+    with_cpu = world == 1 and not args.no_cpu
+    if with_cpu and rank == 0:
+        entry.build_oracles()
+    primary = "sad" if args.workload == "sad" else "lk"
+    res = {}
+    if args.workload in ("lk", "both"):
+        res["lk"] = run_lk_gpu(args, rank, world, local, with_cpu)
+    if args.workload in ("sad", "both"):
+        sad_args = argparse.Namespace(**vars(args))
+        sad_args.steps = args.steps * 10 if args.workload == "both" else args.steps   # SAD steps are ~100x shorter
+        res["sad"] = run_sad_gpu(sad_args, rank, world, local, with_cpu)
+        if res["sad"] is not None:
+            res["sad"]["steps"] = sad_args.steps
+    if rank != 0:
+        return
+    p = res[primary]
+    line = {"metric": "frame-pairs/s", "value": p["value"], "unit": "frame-pairs/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": p["dtype"], "data": "synthetic", "config": p["config"], "roofline": p["roofline"],
+            "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
+    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu"):
+        if key in p:
+            line[key] = p[key]
+    if args.workload == "both":
+        s = res["sad"]
+        line["sad"] = {k: s[k] for k in s if k not in ("clocks",)}
+        line["sad"]["metric"], line["sad"]["unit"] = "frame-pairs/s", "frame-pairs/s"
+    print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

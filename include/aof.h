@@ -172,6 +172,13 @@ int aof_lk_calc_flow_batch(aof_lk *h, const uint8_t *imgs, const uint32_t *t_us,
 int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
 			    aof_lk_raw *d_raw, void *cuda_stream);
 
+/* replace OpticalFlowOpenCV::setCameraMatrix / setCameraDistortion (src/flow_opencv.cpp:72-87; note the
+ * reference's argument order k1, k2, k3, p1, p2).  As in the reference, feature positions are undistorted
+ * (cv::undistortPoints + re-projection, :108-119) only once BOTH have been called; applies to all streams. */
+int aof_lk_set_camera_matrix(aof_lk *h, float focal_len_x, float focal_len_y, float principal_point_x,
+			     float principal_point_y);
+int aof_lk_set_camera_distortion(aof_lk *h, float k1, float k2, float k3, float p1, float p2);
+
 /* state read-back for tests: per stream N entries of updateVector, features_current
  * (x, y), prev_corners (x, y) and prev_status.  Any pointer may be NULL. */
 int aof_lk_get_state(aof_lk *h, int32_t *update_vec, float *feat_cur, float *prev_corners, uint8_t *prev_status);
@@ -186,6 +193,14 @@ int aof_lk_track_points(aof_lk *h, const uint8_t *prev, const uint8_t *cur, int 
 			float *next_pts, uint8_t *status);
 /* cv::FAST(bin ROI, 10, nonmax) on all 16 bins of n frames: score[n * w * h], 0 = no keypoint */
 int aof_lk_fast_scores(aof_lk *h, const uint8_t *imgs, int n, uint8_t *score);
+
+/* optional per-kernel timing (CUDA events around every launch of this library; off by default).
+ * aof_timing_read(k, ...) for k in [0, aof_timing_kernels()) waits for the recorded launches and
+ * returns the kernel's name, its summed device time and its launch count since the last reset. */
+void aof_timing_enable(int on);
+void aof_timing_reset(void);
+int aof_timing_kernels(void);
+int aof_timing_read(int kernel, const char **name, double *total_ms, uint64_t *launches);
 
 /* number of kernel launches this library has issued in this process */
 uint64_t aof_launch_count(void);

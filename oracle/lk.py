@@ -45,6 +45,12 @@ def lib():
     L.olk_calc_flow.argtypes = [C.c_void_p, u8p, C.c_uint32, i32p, f32p, f32p]
     L.olk_get_state.argtypes = [C.c_void_p, i32p, f32p, f32p, u8p, i32p]
     L.olk_get_state.restype = None
+    L.olk_set_camera_matrix.argtypes = [C.c_void_p] + [C.c_float] * 4
+    L.olk_set_camera_matrix.restype = None
+    L.olk_set_camera_distortion.argtypes = [C.c_void_p] + [C.c_float] * 5
+    L.olk_set_camera_distortion.restype = None
+    L.olk_undistort.argtypes = [f32p, f32p, f32p]
+    L.olk_undistort.restype = None
     if hasattr(L, "olk_min_eig"):
         L.olk_min_eig.argtypes = [u8p, C.c_int, C.c_int, f32p]
         L.olk_min_eig.restype = None
@@ -131,6 +137,12 @@ class Tracker:
             lib().olk_free(self.h_)
             self.h_ = None
 
+    def set_camera_matrix(self, fx, fy, cx, cy):
+        lib().olk_set_camera_matrix(self.h_, fx, fy, cx, cy)
+
+    def set_camera_distortion(self, k1, k2, k3, p1=0.0, p2=0.0):
+        lib().olk_set_camera_distortion(self.h_, k1, k2, k3, p1, p2)
+
     def calc_flow(self, img, t_us):
         img = np.ascontiguousarray(img, np.uint8)
         assert img.size == self.w * self.h
@@ -150,3 +162,13 @@ class Tracker:
         return {"update_vec": uv, "feat_cur": fc, "prev_corners": pc, "prev_status": ps, "fast_bins": int(diag[0]),
                 "inliers": int(diag[1]), "active": int(diag[2]), "n_prev_corners": int(diag[3]),
                 "px_x": float(diag[4:5].view(np.float32)[0]), "px_y": float(diag[5:6].view(np.float32)[0])}
+
+
+def undistort(cam, dc, pts):
+    """cv::undistortPoints + re-projection of flow_opencv.cpp:108-119; cam=(fx,fy,cx,cy), dc=(k1,k2,p1,p2,k3)."""
+    cam = np.ascontiguousarray(cam, np.float32)
+    dc = np.ascontiguousarray(dc, np.float32)
+    out = np.ascontiguousarray(pts, np.float32).reshape(-1, 2).copy()
+    for i in range(len(out)):
+        lib().olk_undistort(_p(cam, f32p), _p(dc, f32p), _p(out[i:i + 1], f32p))
+    return out

@@ -61,22 +61,27 @@ int olk_pyr_top_level(int w, int h, int win, int max_level)
 void olk_pyr_down(const u8 *src, int w, int h, u8 *dst)
 {
 	const int dw = (w + 1) / 2, dh = (h + 1) / 2;
-	static const int k[5] = {1, 4, 6, 4, 1};
 	int *row = (int *)malloc(sizeof(int) * (size_t)dw * 5);
+	int have[5] = {-1, -1, -1, -1, -1}; /* source row held by each of the 5 ring slots */
 	for (int y = 0; y < dh; y++) {
+		const int *r[5];
 		for (int j = 0; j < 5; j++) {
-			const u8 *s = src + (size_t)reflect101(2 * y + j - 2, h) * w;
-			for (int x = 0; x < dw; x++) {
-				int acc = 0;
-				for (int i = 0; i < 5; i++) acc += k[i] * s[reflect101(2 * x + i - 2, w)];
-				row[j * dw + x] = acc;
+			const int sy = reflect101(2 * y + j - 2, h), slot = sy % 5;
+			int *o = row + (size_t)slot * dw;
+			if (have[slot] != sy) {
+				const u8 *s = src + (size_t)sy * w;
+				for (int x = 0; x < dw; x++) {
+					const int c = 2 * x;
+					if (c >= 2 && c + 2 < w) o[x] = s[c - 2] + 4 * s[c - 1] + 6 * s[c] + 4 * s[c + 1] + s[c + 2];
+					else o[x] = s[reflect101(c - 2, w)] + 4 * s[reflect101(c - 1, w)] + 6 * s[c] + 4 * s[reflect101(c + 1, w)] +
+						    s[reflect101(c + 2, w)];
+				}
+				have[slot] = sy;
 			}
+			r[j] = o;
 		}
-		for (int x = 0; x < dw; x++) {
-			int acc = 0;
-			for (int j = 0; j < 5; j++) acc += k[j] * row[j * dw + x];
-			dst[(size_t)y * dw + x] = (u8)((acc + 128) >> 8);
-		}
+		u8 *d = dst + (size_t)y * dw;
+		for (int x = 0; x < dw; x++) d[x] = (u8)((r[0][x] + 4 * r[1][x] + 6 * r[2][x] + 4 * r[3][x] + r[4][x] + 128) >> 8);
 	}
 	free(row);
 }
@@ -229,21 +234,36 @@ static const int ring_dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -
 static const int ring_dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
 
 /* largest m such that 9 contiguous ring pixels are all brighter than c + (m-1) or all darker than c - (m-1) */
-static int fast_m(const u8 *p, int stride)
+static int fast_m(const u8 *p, const int *off, int thr)
 {
 	int d[25];
 	const int c = p[0];
-	for (int k = 0; k < 16; k++) d[k] = c - p[ring_dy[k] * stride + ring_dx[k]];
+	{ /* a 9-arc always contains two of the four compass points (ring 0, 4, 8, 12) */
+		const int a = c - p[off[0]], b = c - p[off[4]], e = c - p[off[8]], f = c - p[off[12]];
+		if ((a > thr) + (b > thr) + (e > thr) + (f > thr) < 2 && (a < -thr) + (b < -thr) + (e < -thr) + (f < -thr) < 2) return thr;
+	}
+	for (int k = 0; k < 16; k++) d[k] = c - p[off[k]];
+	/* cheap exact reject (what makes cv::FAST fast): a corner needs 9 contiguous ring pixels beyond +-thr */
+	unsigned mp = 0, mn = 0;
+	for (int k = 0; k < 16; k++) { mp |= (unsigned)(d[k] > thr) << k; mn |= (unsigned)(d[k] < -thr) << k; }
+	int corner = 0;
+	for (int pass = 0; pass < 2 && !corner; pass++) {
+		unsigned m = pass ? mn : mp;
+		m |= m << 16;
+		const unsigned a = m & (m >> 1), b = a & (a >> 2), e = b & (b >> 4);
+		corner = (e & (m >> 8) & 0xFFFFu) != 0;
+	}
+	if (!corner) return thr; /* not a corner: any value <= thr */
 	for (int k = 16; k < 25; k++) d[k] = d[k - 16];
 	int m = -1000;
 	for (int k = 0; k < 16; k++) {
-		int mn = d[k], mx = d[k];
+		int mn9 = d[k], mx9 = d[k];
 		for (int i = 1; i < 9; i++) {
-			if (d[k + i] < mn) mn = d[k + i];
-			if (d[k + i] > mx) mx = d[k + i];
+			if (d[k + i] < mn9) mn9 = d[k + i];
+			if (d[k + i] > mx9) mx9 = d[k + i];
 		}
-		if (mn > m) m = mn;
-		if (-mx > m) m = -mx;
+		if (mn9 > m) m = mn9;
+		if (-mx9 > m) m = -mx9;
 	}
 	return m;
 }
@@ -257,10 +277,12 @@ static int fast_m(const u8 *p, int stride)
 int olk_fast(const u8 *roi, int stride, int w, int h, int thr, u8 *score)
 {
 	u8 *raw = (u8 *)calloc((size_t)w * h, 1);
+	int off[16];
+	for (int k = 0; k < 16; k++) off[k] = ring_dy[k] * stride + ring_dx[k];
 	memset(score, 0, (size_t)w * h);
 	for (int y = 3; y < h - 3; y++)
 		for (int x = 3; x < w - 3; x++) {
-			const int m = fast_m(roi + (size_t)y * stride + x, stride);
+			const int m = fast_m(roi + (size_t)y * stride + x, off, thr);
 			if (m > thr) raw[y * w + x] = (u8)(m - 1);
 		}
 	int n = 0;
@@ -304,6 +326,10 @@ typedef struct olk_tracker {
 	int have_feat_prev;
 	/* limiter, per object (optical_flow.cpp:55 static made per stream) */
 	float sum_x, sum_y; int sum_q, n_valid; uint32_t t_last;
+	/* flow_opencv.cpp:72-87: camera model, used only when both setters were called */
+	int have_cam, have_dist;
+	float cam[4];  /* fx, fy, cx, cy */
+	float dc[5];   /* k1, k2, p1, p2, k3 */
 	/* diagnostics of the last call */
 	int last_fast_bins, last_inliers, last_active;
 	float last_px_x, last_px_y;
@@ -502,7 +528,41 @@ static int limit_rate(olk_tracker *t, int q, uint32_t t_us, int *dt_us, float *f
 	return -1;
 }
 
-/* flow_opencv.cpp:89-210 (the undistortPoints branch :108-119 is off, as in aero) */
+void olk_set_camera_matrix(olk_tracker *t, float fx, float fy, float cx, float cy)
+{
+	t->cam[0] = fx; t->cam[1] = fy; t->cam[2] = cx; t->cam[3] = cy; t->have_cam = 1;
+}
+
+/* argument order of OpticalFlowOpenCV::setCameraDistortion(k1, k2, k3, p1, p2) */
+void olk_set_camera_distortion(olk_tracker *t, float k1, float k2, float k3, float p1, float p2)
+{
+	t->dc[0] = k1; t->dc[1] = k2; t->dc[2] = p1; t->dc[3] = p2; t->dc[4] = k3; t->have_dist = 1;
+}
+
+/* cv::undistortPoints(src, dst, K, D) (no R, no P; 5 fixed-point iterations, in double) followed by the
+ * re-projection of flow_opencv.cpp:113-118 (in float) */
+void olk_undistort(const float cam[4], const float dc[5], float *pt)
+{
+	const double fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3];
+	const double k1 = dc[0], k2 = dc[1], p1 = dc[2], p2 = dc[3], k3 = dc[4];
+	const double ifx = 1. / fx, ify = 1. / fy;
+	const double u = pt[0], v = pt[1];
+	double x = (u - cx) * ifx, y = (v - cy) * ify;
+	const double x0 = x, y0 = y;
+	for (int j = 0; j < 5; j++) {
+		const double r2 = x * x + y * y;
+		const double icdist = (1 + ((0 * r2 + 0) * r2 + 0) * r2) / (1 + ((k3 * r2 + k2) * r2 + k1) * r2);
+		if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+		const double dx = 2 * p1 * x * y + p2 * (r2 + 2 * x * x) + 0 * r2 + 0 * r2 * r2;
+		const double dy = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y + 0 * r2 + 0 * r2 * r2;
+		x = (x0 - dx) * icdist; y = (y0 - dy) * icdist;
+	}
+	const float xf = (float)x, yf = (float)y;
+	pt[0] = xf * cam[0] + cam[2];
+	pt[1] = yf * cam[1] + cam[3];
+}
+
+/* flow_opencv.cpp:89-210 */
 int olk_calc_flow(olk_tracker *t, const u8 *img, uint32_t t_us, int *dt_us, float *flow_x, float *flow_y)
 {
 	const int N = t->n_feat;
@@ -513,6 +573,8 @@ int olk_calc_flow(olk_tracker *t, const u8 *img, uint32_t t_us, int *dt_us, floa
 	int meancount = 0;
 	float mx = 0.f, my = 0.f, sx = 0.f, sy = 0.f;
 	track_features(t, img, t->feat_cur, t->update_vec);
+	if (t->have_cam && t->have_dist)
+		for (int i = 0; i < N; i++) olk_undistort(t->cam, t->dc, &t->feat_cur[2 * i]);
 	int *uv = t->update_vec;
 	const float *c = t->feat_cur, *p = t->feat_prev;
 	t->last_active = 0;

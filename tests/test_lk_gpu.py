@@ -188,3 +188,21 @@ def test_reset_and_errors(pkg):
         pkg.LkFlow(FX, FY, -1, 64, 64, num_features=101)
     with pytest.raises(pkg.AofError):
         pkg.LkFlow(FX, FY, -1, 8, 8)
+
+
+def test_undistort_branch_matches_oracle(pkg):
+    """setCameraMatrix + setCameraDistortion switch on cv::undistortPoints (flow_opencv.cpp:108-119)."""
+    w = h = 128
+    fr = pkg.synth.lk_sequence(7, w, h, -2, 3, seed=77)
+    f = pkg.LkFlow(FX, FY, -1, w, h, 20)
+    o = olk.Tracker(FX, FY, -1, w, h, 20)
+    f.set_camera_matrix(FX, FY, 64.0, 64.0)
+    o.set_camera_matrix(FX, FY, 64.0, 64.0)
+    r0 = f.calc_flow(fr[0], 1000)                    # only one setter called: still the plain path
+    assert r0 == o.calc_flow(fr[0], 1000)
+    f.set_camera_distortion(-0.2, 0.05, 0.01, 0.001, -0.002)
+    o.set_camera_distortion(-0.2, 0.05, 0.01, 0.001, -0.002)
+    for k in range(1, 7):
+        assert f.calc_flow(fr[k], 1000 + 9000 * k) == o.calc_flow(fr[k], 1000 + 9000 * k), k
+        check_state(f.state(), 0, o.state())
+    f.close()

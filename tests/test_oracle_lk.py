@@ -125,3 +125,28 @@ def test_calcflow_vs_cv2_restatement_live(pkg):
             rb = B.calc_flow(fr[k], 1000 + 13333 * k)
             assert ra[0] == rb[0] and list(A.state()["update_vec"]) == B.update
             assert abs(ra[2] - rb[2]) <= ANG_TOL and abs(ra[3] - rb[3]) <= ANG_TOL
+
+
+@pytest.mark.skipif(cv2 is None, reason="cv2 not importable")
+def test_undistort_vs_cv2_live():
+    rng = np.random.default_rng(0)
+    for cam, dc in [((216.6677, 216.2457, 64, 64), (-0.2, 0.05, 0.001, -0.002, 0.01)),
+                    ((500.5, 498.1, 320.2, 239.7), (0.12, -0.3, 0.0, 0.0, 0.2)), ((216, 216, 64, 64), (0, 0, 0, 0, 0))]:
+        pts = np.concatenate([rng.uniform(-20, 700, (300, 2)), [[-100, -100]]]).astype(np.float32)
+        K = np.array([[cam[0], 0, cam[2]], [0, cam[1], cam[3]], [0, 0, 1]], np.float32)
+        u = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, np.array([dc], np.float32)).reshape(-1, 2)
+        want = np.stack([u[:, 0] * np.float32(cam[0]) + np.float32(cam[2]), u[:, 1] * np.float32(cam[1]) + np.float32(cam[3])], 1)
+        assert np.array_equal(olk_undistort(cam, dc, pts), want.astype(np.float32))
+
+
+def olk_undistort(cam, dc, pts):
+    return lk.undistort(cam, dc, pts)
+
+
+def test_undistort_known_answers():
+    # identity distortion is the identity map up to the float round trip; golden values for a distorted camera
+    cam, dc = (216.6677, 216.2457, 64.0, 64.0), (-0.2, 0.05, 0.001, -0.002, 0.01)
+    pts = np.array([[64, 64], [0, 0], [127, 127], [-100, -100], [100.5, 20.25]], np.float32)
+    assert np.abs(lk.undistort(cam, (0, 0, 0, 0, 0), pts) - pts).max() < 1e-4
+    got = lk.undistort(cam, dc, pts)
+    assert np.array_equal(got[0], [64, 64]) and (np.abs(got[1:] - pts[1:]).max(1) > 0.01).all()
