@@ -73,6 +73,117 @@ cudaError_t lk_pyr_down_launch(const uint8_t *src, uint8_t *dst, int sw, int sh,
 }
 
 // ---------------------------------------------------------------------------
+// K3 fused: levels 1, 2 and 3 of one frame in ONE pass over level 0 (the HBM-bound part of the
+// LK path: 307 200 B read + 100 800 B written per 640 x 480 frame).  CTA = one 16 x 8 tile of
+// level 3 with the level-2 / level-1 / level-0 regions it depends on (35 x 19, 73 x 41, 149 x 85)
+// staged in shared memory; the halo re-reads of level 0 (1.55x) are L2 hits from the neighbouring
+// CTAs.  Each level uses cv::pyrDown's own BORDER_REFLECT_101 on ITS size, so tiles are addressed
+// by unreflected coordinate and every tap is reflected explicitly (an even-sized level does not
+// commute with reflecting the level below).
+constexpr int PF3W = 16, PF3H = 8;
+constexpr int PF2W = 2 * PF3W + 3, PF2H = 2 * PF3H + 3;   // 35 x 19
+constexpr int PF1W = 2 * PF2W + 3, PF1H = 2 * PF2H + 3;   // 73 x 41
+constexpr int PF0W = 2 * PF1W + 3, PF0H = 2 * PF1H + 3;   // 149 x 85
+constexpr int PF0P = 152;                                  // level-0 tile pitch: column 0 <-> x = o0 - 2 (8-aligned)
+constexpr int PF_THREADS = 256;
+
+// one pyrDown from a source tile to a destination tile, both in shared memory.
+// tile element [r][c] <-> level coordinate (oy + r, ox + c); only coordinates inside the level are valid.
+__device__ __forceinline__ void pf_down(const uint8_t *src, int sp, int sox, int soy, int slw, int slh, int sth,
+					uint8_t *dst, int dp, int dox, int doy, int dlw, int dlh, int dtw, int dth, uint16_t *tmp)
+{
+	const int tid = threadIdx.x;
+	for (int i = tid; i < sth * dtw; i += PF_THREADS) {
+		const int r = i / dtw, c = i - r * dtw;
+		const int y = soy + r, X = dox + c;
+		if (y < 0 || y >= slh || X < 0 || X >= dlw) continue;
+		const uint8_t *row = src + r * sp - sox;
+		const int x = 2 * X;
+		int v;
+		if (x >= 2 && x + 2 < slw) v = row[x - 2] + 4 * row[x - 1] + 6 * row[x] + 4 * row[x + 1] + row[x + 2];
+		else v = row[reflect101(x - 2, slw)] + 4 * row[reflect101(x - 1, slw)] + 6 * row[x] + 4 * row[reflect101(x + 1, slw)] +
+			 row[reflect101(x + 2, slw)];
+		tmp[i] = (uint16_t)v;
+	}
+	__syncthreads();
+	for (int i = tid; i < dth * dtw; i += PF_THREADS) {
+		const int r = i / dtw, c = i - r * dtw;
+		const int Y = doy + r, X = dox + c;
+		if (Y < 0 || Y >= dlh || X < 0 || X >= dlw) continue;
+		const int y = 2 * Y;
+		const uint16_t *col = tmp + c - soy * dtw;
+		int v;
+		if (y >= 2 && y + 2 < slh) v = col[(y - 2) * dtw] + 4 * col[(y - 1) * dtw] + 6 * col[y * dtw] + 4 * col[(y + 1) * dtw] + col[(y + 2) * dtw];
+		else v = col[reflect101(y - 2, slh) * dtw] + 4 * col[reflect101(y - 1, slh) * dtw] + 6 * col[y * dtw] +
+			 4 * col[reflect101(y + 1, slh) * dtw] + col[reflect101(y + 2, slh) * dtw];
+		dst[r * dp + c] = (uint8_t)((v + 128) >> 8);
+	}
+	__syncthreads();
+}
+
+// copy the core [cx, cx + cw) x [cy, cy + ch) of a tile (tile coordinates) to its level image
+__device__ __forceinline__ void pf_store(const uint8_t *tile, int tp, int ox, int oy, int cx, int cy, int cw, int ch,
+					 uint8_t *img, int lw, int lh)
+{
+	for (int i = threadIdx.x; i < cw * ch; i += PF_THREADS) {
+		const int r = i / cw, c = i - r * cw;
+		const int x = ox + cx + c, y = oy + cy + r;
+		if (x < lw && y < lh) img[(size_t)y * lw + x] = tile[(cy + r) * tp + cx + c];
+	}
+}
+
+template <bool ALIGNED>
+__global__ void __launch_bounds__(PF_THREADS)
+lk_pyr_fused_kernel(LkGeom g, const uint8_t *__restrict__ l0, uint8_t *__restrict__ l1, uint8_t *__restrict__ l2,
+		    uint8_t *__restrict__ l3)
+{
+	__shared__ __align__(16) uint8_t s0[PF0H * PF0P];
+	__shared__ uint16_t s_tmp[PF0H * PF1W];
+	__shared__ uint8_t s1[PF1H * PF1W], s2[PF2H * PF2W], s3[PF3H * PF3W];
+	const size_t stream = blockIdx.z;
+	const int o3x = blockIdx.x * PF3W, o3y = blockIdx.y * PF3H;
+	const int o2x = 2 * o3x - 2, o2y = 2 * o3y - 2, o1x = 2 * o2x - 2, o1y = 2 * o2y - 2, o0x = 2 * o1x - 2, o0y = 2 * o1y - 2;
+	const int w0 = g.w[0], h0 = g.h[0];
+	const uint8_t *img = l0 + stream * (size_t)w0 * h0;
+	const int bx = o0x - 2; // tile column 0, a multiple of 8
+	if (ALIGNED) {
+		for (int i = threadIdx.x; i < PF0H * (PF0P / 4); i += PF_THREADS) {
+			const int r = i / (PF0P / 4), q = i - r * (PF0P / 4);
+			const int y = o0y + r, x = bx + 4 * q;
+			if (y >= 0 && y < h0 && x >= 0 && x < w0)
+				reinterpret_cast<uint32_t *>(s0)[r * (PF0P / 4) + q] = __ldg(reinterpret_cast<const uint32_t *>(img + (size_t)y * w0 + x));
+		}
+	} else {
+		for (int i = threadIdx.x; i < PF0H * PF0P; i += PF_THREADS) {
+			const int r = i / PF0P, c = i - r * PF0P;
+			const int y = o0y + r, x = bx + c;
+			if (y >= 0 && y < h0 && x >= 0 && x < w0) s0[i] = img[(size_t)y * w0 + x];
+		}
+	}
+	__syncthreads();
+	pf_down(s0, PF0P, bx, o0y, w0, h0, PF0H, s1, PF1W, o1x, o1y, g.w[1], g.h[1], PF1W, PF1H, s_tmp);
+	pf_down(s1, PF1W, o1x, o1y, g.w[1], g.h[1], PF1H, s2, PF2W, o2x, o2y, g.w[2], g.h[2], PF2W, PF2H, s_tmp);
+	pf_down(s2, PF2W, o2x, o2y, g.w[2], g.h[2], PF2H, s3, PF3W, o3x, o3y, g.w[3], g.h[3], PF3W, PF3H, s_tmp);
+	pf_store(s1, PF1W, o1x, o1y, 6, 6, 4 * PF3W, 4 * PF3H, l1 + stream * (size_t)g.w[1] * g.h[1], g.w[1], g.h[1]);
+	pf_store(s2, PF2W, o2x, o2y, 2, 2, 2 * PF3W, 2 * PF3H, l2 + stream * (size_t)g.w[2] * g.h[2], g.w[2], g.h[2]);
+	pf_store(s3, PF3W, o3x, o3y, 0, 0, PF3W, PF3H, l3 + stream * (size_t)g.w[3] * g.h[3], g.w[3], g.h[3]);
+}
+
+// levels 1..3 of n frames (only for a 4-level pyramid)
+cudaError_t lk_pyr_fused_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1, uint8_t *l2, uint8_t *l3, int n, cudaStream_t st)
+{
+	if (n <= 0) return cudaSuccess;
+	dim3 grid((g.w[3] + PF3W - 1) / PF3W, (g.h[3] + PF3H - 1) / PF3H, n);
+	KernelTimer kt(KID_LK_PYR_FUSED, st);
+	if (g.w[0] % 4 == 0 && (reinterpret_cast<uintptr_t>(l0) & 3) == 0 && ((size_t)g.w[0] * g.h[0]) % 4 == 0)
+		lk_pyr_fused_kernel<true><<<grid, PF_THREADS, 0, st>>>(g, l0, l1, l2, l3);
+	else
+		lk_pyr_fused_kernel<false><<<grid, PF_THREADS, 0, st>>>(g, l0, l1, l2, l3);
+	count_launch();
+	return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
 // K6: pyramidal LK of one point by one warp.
 // Per-warp scratch in shared memory.
 struct LkWarpScratch {
@@ -328,54 +439,65 @@ cudaError_t lk_track_points_launch(const LkGeom &g, const LkPyr &prev, const LkP
 
 // ---------------------------------------------------------------------------
 // K4: FAST-9/16 score + 3x3 non-max suppression with cv::FAST semantics on each
-// bin ROI as a stand-alone image.  CTA = 32 x 16 pixels of one bin.
-constexpr int FT_TW = 32, FT_TH = 16;
+// bin ROI as a stand-alone image.  CTA = 32 x 24 pixels of one bin
+// (a 160 x 120 bin is exactly 5 x 5 tiles).
+//
+// The response of EVERY pixel is computed exactly and branch-free, two horizontally
+// adjacent pixels per thread in u16x2 lanes: with D_k = c - ring_k + 256 (no borrow
+// between the lanes), the response is  max_arcs(min_9 D) - 257  (dark arcs) or
+// 255 - min_arcs(max_9 D)  (bright arcs); the sliding 9-windows are two levels of
+// VIMNMX3.U16x2 (3-input packed min / max).  On textures where a third of the pixels
+// are corners (the LK benchmark texture) a test-then-score scheme diverges on almost
+// every warp; this one does 1/2.7 of the instructions of the scalar version.
+// Materialised max3/min3 only: ptxas 12.9 drops the negation when max(m, -x) is
+// folded into VIMNMX3 (tools/ptxas_vimnmx3_neg_repro.cu).
+constexpr int FT_TW = 32, FT_TH = 24;
+constexpr int FT_PW = FT_TW + 8, FT_PH = FT_TH + 8;   // pixel tile 40 x 32
+constexpr int FT_SW = FT_TW + 2, FT_SH = FT_TH + 2;   // score tile 34 x 26
+constexpr int FT_PAIRS = FT_SW / 2;                    // 17 pixel pairs per score row
 
-__device__ __forceinline__ bool has_arc9(unsigned m)
-{
-	m |= m << 16;
-	const unsigned a = m & (m >> 1), b = a & (a >> 2), c = b & (b >> 4);
-	return (c & (m >> 8) & 0xFFFFu) != 0;
-}
+__device__ __forceinline__ uint32_t mn3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u16x2(a, b, c); }
+__device__ __forceinline__ uint32_t mx3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
 
-// p -> centre pixel in a shared tile of row pitch `pitch`; returns the response (0 = not a corner)
-__device__ __forceinline__ int fast_score(const uint8_t *p, int pitch, int thr)
+// pairs A[r][j] = (px[2j], px[2j+1]), B[r][j] = (px[2j+1], px[2j+2]) as u16x2; `row` -> A or B row r,
+// `j` the pair index of the CENTRE pair in B (centre columns are odd: c = 2j + 1)
+__device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (*A)[FT_PW / 2], const uint32_t (*B)[FT_PW / 2], int r, int j)
 {
-	const int c = p[0];
-	int d[16];
-	d[0] = c - p[3 * pitch];      d[1] = c - p[3 * pitch + 1];  d[2] = c - p[2 * pitch + 2];  d[3] = c - p[pitch + 3];
-	d[4] = c - p[3];              d[5] = c - p[-pitch + 3];     d[6] = c - p[-2 * pitch + 2]; d[7] = c - p[-3 * pitch + 1];
-	d[8] = c - p[-3 * pitch];     d[9] = c - p[-3 * pitch - 1]; d[10] = c - p[-2 * pitch - 2]; d[11] = c - p[-pitch - 3];
-	d[12] = c - p[-3];            d[13] = c - p[pitch - 3];     d[14] = c - p[2 * pitch - 2]; d[15] = c - p[3 * pitch - 1];
-	unsigned mp = 0, mn = 0;
-#pragma unroll
-	for (int k = 0; k < 16; k++) { mp |= (unsigned)(d[k] > thr) << k; mn |= (unsigned)(d[k] < -thr) << k; }
-	if (!has_arc9(mp) && !has_arc9(mn)) return 0;
-	// exact response: max over the 16 arcs of max(min d, min e), e = -d, minus 1.
-	// (e is materialised: ptxas 12.9 drops the negation when it folds max(m, -hi9) into VIMNMX3 on sm_100a.)
-	int e[16];
-#pragma unroll
-	for (int k = 0; k < 16; k++) e[k] = -d[k];
-	int d2[16], e2[16], d4[16], e4[16];
-#pragma unroll
-	for (int k = 0; k < 16; k++) { d2[k] = min(d[k], d[(k + 1) & 15]); e2[k] = min(e[k], e[(k + 1) & 15]); }
-#pragma unroll
-	for (int k = 0; k < 16; k++) { d4[k] = min(d2[k], d2[(k + 2) & 15]); e4[k] = min(e2[k], e2[(k + 2) & 15]); }
-	int m = -1000;
+	const uint32_t cb = B[r][j] + 0x01000100u;
+	uint32_t D[16];
+	// ring offsets (dx, dy); odd dx -> even start column -> A, even dx -> B.  start column = 2j + 1 + dx
+	D[0] = cb - B[r + 3][j];         D[1] = cb - A[r + 3][j + 1];   D[2] = cb - B[r + 2][j + 1];  D[3] = cb - A[r + 1][j + 2];
+	D[4] = cb - A[r][j + 2];         D[5] = cb - A[r - 1][j + 2];   D[6] = cb - B[r - 2][j + 1];  D[7] = cb - A[r - 3][j + 1];
+	D[8] = cb - B[r - 3][j];         D[9] = cb - A[r - 3][j];       D[10] = cb - B[r - 2][j - 1]; D[11] = cb - A[r - 1][j - 1];
+	D[12] = cb - A[r][j - 1];        D[13] = cb - A[r + 1][j - 1];  D[14] = cb - B[r + 2][j - 1]; D[15] = cb - A[r + 3][j];
+	uint32_t lo3[16], hi3[16];
 #pragma unroll
 	for (int k = 0; k < 16; k++) {
-		const int d9 = min(min(d4[k], d4[(k + 4) & 15]), d[(k + 8) & 15]);
-		const int e9 = min(min(e4[k], e4[(k + 4) & 15]), e[(k + 8) & 15]);
-		m = max(m, max(d9, e9));
+		lo3[k] = mn3(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
+		hi3[k] = mx3(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
 	}
-	return m - 1;
+	uint32_t lo9[16], hi9[16];
+#pragma unroll
+	for (int k = 0; k < 16; k++) {
+		lo9[k] = mn3(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+		hi9[k] = mx3(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+	}
+	uint32_t dark = mx3(lo9[0], lo9[1], lo9[2]), bright = mn3(hi9[0], hi9[1], hi9[2]);
+#pragma unroll
+	for (int k = 3; k < 15; k += 2) { dark = mx3(dark, lo9[k], lo9[k + 1]); bright = mn3(bright, hi9[k], hi9[k + 1]); }
+	dark = __vmaxu2(dark, lo9[15]); bright = __vminu2(bright, hi9[15]);
+	return __vmaxu2(dark, 0x02000200u - bright); // per lane: m + 256
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int FT_THREADS = 224; // 442 pixel pairs per tile = 2 rounds of 221
+
+// ALIGNED: W % 16 == 0 and the frame base is 4-byte aligned, so every tile row starts on a word
+template <bool ALIGNED>
+__global__ void __launch_bounds__(FT_THREADS)
 lk_fast_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int tiles_x, int tiles_y)
 {
-	__shared__ uint8_t s_pix[FT_TH + 8][FT_TW + 8];
-	__shared__ uint8_t s_score[FT_TH + 2][FT_TW + 2];
+	__shared__ __align__(8) uint32_t s_A[FT_PH][FT_PW / 2], s_B[FT_PH][FT_PW / 2];
+	__shared__ uint8_t s_score[FT_SH][FT_SW + 2];
 	const size_t stream = blockIdx.y;
 	const int per_bin = tiles_x * tiles_y;
 	const int bin = blockIdx.x / per_bin, t = blockIdx.x - bin * per_bin;
@@ -384,28 +506,49 @@ lk_fast_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__r
 	const int W = g.w[0], H = g.h[0], bw = g.bw, bh = g.bh;
 	const int c0 = (bin >> 2) * bw, r0 = (bin & 3) * bh;      // bin = x * 4 + y
 	const int x0 = tx * FT_TW, y0 = ty * FT_TH;                // tile origin inside the bin
-	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
+	const uint8_t *img = l0 + stream * (size_t)W * H;
 	const int tid = threadIdx.x;
-	for (int i = tid; i < (FT_TH + 8) * (FT_TW + 8); i += 256) {
-		const int r = i / (FT_TW + 8), c = i - r * (FT_TW + 8);
-		const int y = min(max(y0 - 4 + r, 0), bh - 1), x = min(max(x0 - 4 + c, 0), bw - 1);
-		s_pix[r][c] = img[(size_t)y * W + x];
+	// pixels (x0 - 4 .. x0 + 35, y0 - 4 .. y0 + 27) of the bin as u16x2 pairs.  Pixels outside the bin (read from
+	// the neighbouring bins, clamped at the image border) only ever reach positions that are not tested.
+	for (int i = tid; i < FT_PH * (FT_PW / 4); i += FT_THREADS) {
+		const int r = i / (FT_PW / 4), q = i - r * (FT_PW / 4);
+		const int y = min(max(r0 + y0 - 4 + r, 0), H - 1);
+		uint32_t p0, p1, p2, p3, p4;
+		if (ALIGNED) {
+			const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (size_t)y * W);
+			const int wq = (c0 + x0 - 4) / 4 + q, wmax = W / 4 - 1;
+			const uint32_t w0 = __ldg(row + min(max(wq, 0), wmax)), w1 = __ldg(row + min(max(wq + 1, 0), wmax));
+			p0 = w0 & 0xFF; p1 = (w0 >> 8) & 0xFF; p2 = (w0 >> 16) & 0xFF; p3 = w0 >> 24; p4 = w1 & 0xFF;
+		} else {
+			const uint8_t *row = img + (size_t)y * W;
+			const int x = c0 + x0 - 4 + 4 * q;
+			p0 = row[min(max(x, 0), W - 1)]; p1 = row[min(max(x + 1, 0), W - 1)]; p2 = row[min(max(x + 2, 0), W - 1)];
+			p3 = row[min(max(x + 3, 0), W - 1)]; p4 = row[min(max(x + 4, 0), W - 1)];
+		}
+		*reinterpret_cast<uint2 *>(&s_A[r][2 * q]) = make_uint2(p0 | (p1 << 16), p2 | (p3 << 16));
+		*reinterpret_cast<uint2 *>(&s_B[r][2 * q]) = make_uint2(p1 | (p2 << 16), p3 | (p4 << 16));
 	}
 	__syncthreads();
-	for (int i = tid; i < (FT_TH + 2) * (FT_TW + 2); i += 256) {
-		const int r = i / (FT_TW + 2), c = i - r * (FT_TW + 2);
-		const int y = y0 - 1 + r, x = x0 - 1 + c;
-		int sc = 0;
-		if (x >= 3 && x < bw - 3 && y >= 3 && y < bh - 3) sc = fast_score(&s_pix[r + 3][c + 3], FT_TW + 8, g.fast_thr);
-		s_score[r][c] = (uint8_t)sc;
+	// scores of columns x0 - 1 .. x0 + 32 (tile columns 3 .. 36), rows y0 - 1 .. y0 + 24 (tile rows 3 .. 28)
+	const uint32_t lim = 256u + (uint32_t)g.fast_thr;
+	for (int i = tid; i < FT_SH * FT_PAIRS; i += FT_THREADS) {
+		const int r = i / FT_PAIRS, jp = i - r * FT_PAIRS;
+		const int y = y0 - 1 + r, x = x0 - 1 + 2 * jp;
+		uint32_t sc0 = 0, sc1 = 0;
+		if (y >= 3 && y < bh - 3 && x + 1 >= 3 && x < bw - 3) {
+			const uint32_t m = fast_score_pair(s_A, s_B, r + 3, jp + 1); // centre columns 2 (jp + 1) + 1 = 3 + 2 jp
+			const uint32_t m0 = m & 0xFFFFu, m1 = m >> 16;
+			if (x >= 3 && m0 > lim) sc0 = m0 - 257u;
+			if (x + 1 < bw - 3 && m1 > lim) sc1 = m1 - 257u;
+		}
+		*reinterpret_cast<uint16_t *>(&s_score[r][2 * jp]) = (uint16_t)(sc0 | (sc1 << 8));
 	}
 	__syncthreads();
-	for (int i = tid; i < FT_TH * FT_TW; i += 256) {
-		const int r = i / FT_TW, c = i - r * FT_TW;
+	for (int i = tid; i < FT_TH * FT_TW; i += FT_THREADS) {
+		const int r = i >> 5, c = i & 31;
 		const int y = y0 + r, x = x0 + c;
-		if (x >= bw || y >= bh) continue;
 		const int v = s_score[r + 1][c + 1];
-		if (!v) continue;
+		if (!v || x >= bw || y >= bh) continue;
 		const bool keep = v > s_score[r][c] && v > s_score[r][c + 1] && v > s_score[r][c + 2] && v > s_score[r + 1][c] &&
 				  v > s_score[r + 1][c + 2] && v > s_score[r + 2][c] && v > s_score[r + 2][c + 1] &&
 				  v > s_score[r + 2][c + 2];
@@ -425,7 +568,10 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 	const int tiles_x = (g.bw + FT_TW - 1) / FT_TW, tiles_y = (g.bh + FT_TH - 1) / FT_TH;
 	dim3 grid(tiles_x * tiles_y * LK_BINS, n);
 	KernelTimer kt(KID_LK_FAST, st);
-	lk_fast_kernel<<<grid, 256, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
+	if (g.w[0] % 16 == 0 && (reinterpret_cast<uintptr_t>(l0) & 3) == 0)
+		lk_fast_kernel<true><<<grid, FT_THREADS, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
+	else
+		lk_fast_kernel<false><<<grid, FT_THREADS, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
 	count_launch();
 	return cudaGetLastError();
 }
