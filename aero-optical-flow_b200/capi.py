@@ -43,6 +43,14 @@ class LkParams(C.Structure):
 lk_raw_dtype = np.dtype([("px_x", np.float32), ("px_y", np.float32), ("inliers", np.int32), ("active", np.int32),
                          ("fast_bins", np.int32), ("quality", np.int32)])
 
+class DenseParams(C.Structure):
+    _fields_ = [("image_width", C.c_int), ("image_height", C.c_int), ("search_size", C.c_int),
+                ("flow_feature_threshold", C.c_int), ("flow_value_threshold", C.c_int)]
+
+
+dense_block_dtype = np.dtype([("dx", np.int16), ("dy", np.int16), ("subdir", np.int16), ("flags", np.int16),
+                              ("best_sad", np.uint32), ("texture", np.uint32)])
+
 _lib = None
 
 
@@ -89,6 +97,12 @@ def lib():
     L.aof_lk_pyramid.argtypes = [vp, u8p, C.c_int, vp, vp, vp]
     L.aof_lk_track_points.argtypes = [vp, u8p, u8p, C.c_int, vp, C.c_int, vp, vp]
     L.aof_lk_fast_scores.argtypes = [vp, u8p, C.c_int, vp]
+    L.aof_sad_dense_create.argtypes = [C.POINTER(DenseParams), C.c_int, C.POINTER(vp)]
+    L.aof_sad_dense_destroy.argtypes = [vp]
+    L.aof_sad_dense_destroy.restype = None
+    L.aof_sad_dense_grid.argtypes = [vp, ip, ip, ip, ip]
+    L.aof_sad_dense_compute.argtypes = [vp, u8p, u8p, C.c_int, vp]
+    L.aof_sad_dense_compute_device.argtypes = [vp, u8p, u8p, C.c_int, vp, vp]
     _lib = L
     return L
 
@@ -260,3 +274,35 @@ class LkFlow:
         sc = np.zeros_like(imgs)
         check(lib().aof_lk_fast_scores(self.handle, _ptr(imgs), len(imgs), _ptr(sc)), "aof_lk_fast_scores")
         return sc
+
+
+class SadDense:
+    """dense per-block SAD flow field (aof_sad_dense_*)."""
+
+    def __init__(self, width, height, search=8, feat_thr=30, val_thr=3000, device=0):
+        self.params = DenseParams(width, height, search, feat_thr, val_thr)
+        self.w, self.h = width, height
+        self.handle = C.c_void_p()
+        check(lib().aof_sad_dense_create(C.byref(self.params), device, C.byref(self.handle)), "aof_sad_dense_create")
+        g = [C.c_int() for _ in range(4)]
+        lib().aof_sad_dense_grid(self.handle, *[C.byref(x) for x in g])
+        self.nbx, self.nby, self.x0, self.y0 = [x.value for x in g]
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib().aof_sad_dense_destroy(self.handle)
+            self.handle = None
+
+    __del__ = close
+
+    def compute(self, prev, cur):
+        prev = np.ascontiguousarray(prev, np.uint8).reshape(-1, self.h, self.w)
+        cur = np.ascontiguousarray(cur, np.uint8).reshape(-1, self.h, self.w)
+        n = len(prev)
+        out = np.zeros((n, self.nby, self.nbx), dense_block_dtype)
+        check(lib().aof_sad_dense_compute(self.handle, _ptr(prev), _ptr(cur), n, _ptr(out)), "aof_sad_dense_compute")
+        return out
+
+    def compute_device(self, d_prev, d_cur, n, d_field, stream=0):
+        check(lib().aof_sad_dense_compute_device(self.handle, d_prev, d_cur, n, d_field, stream or None),
+              "aof_sad_dense_compute_device")

@@ -146,3 +146,17 @@ cudaError_t lk_track_points_launch(const LkGeom &g, const LkPyr &prev, const LkP
 				   float2 *out, uint8_t *status, int n, cudaStream_t st);
 
 } // namespace aof
+
+// ---------------------------------------------------------------------------
+// dense SAD field (BASELINE config 4)
+namespace aof {
+struct DenseGeom {
+	int width, height;
+	size_t frame_stride;
+	int i_lo, i_hi, j_lo, j_hi; // lattice indices (block origin = 8 * index) whose search window + 1 px lies inside the image
+	int nbx, nby;
+	uint32_t feat_thr, val_thr;
+};
+cudaError_t sad_dense_launch(int search, const uint8_t *prev, const uint8_t *cur, const DenseGeom &g, int n,
+			     aof_dense_block *field, cudaStream_t st);
+} // namespace aof

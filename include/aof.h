@@ -194,6 +194,40 @@ int aof_lk_track_points(aof_lk *h, const uint8_t *prev, const uint8_t *cur, int 
 /* cv::FAST(bin ROI, 10, nonmax) on all 16 bins of n frames: score[n * w * h], 0 = no keypoint */
 int aof_lk_fast_scores(aof_lk *h, const uint8_t *imgs, int n, uint8_t *score);
 
+/* ------------------------------------------------------------ dense SAD field */
+
+/* Per-block flow field over every 8x8 block of the 8-px lattice whose search window (+ the 1-px
+ * sub-pixel halo) lies inside the image: the reference's per-block primitives compute_diff
+ * (src/px4flow.cpp:114), compute_sad_8x8 (:300, search order :394-405) and compute_subpixel (:155,
+ * direction choice :413-422) with 32-bit offsets, for images the reference itself cannot address
+ * (BASELINE config 4: 1280x720, +-8). */
+typedef struct aof_dense_params {
+	int image_width, image_height; /* width a multiple of 4 */
+	int search_size;               /* 4, 6 or 8 */
+	int flow_feature_threshold;    /* texture gate (30) */
+	int flow_value_threshold;      /* SAD acceptance (3000) */
+} aof_dense_params;
+
+typedef struct aof_dense_block {
+	int16_t dx, dy;    /* arg-min displacement (valid when flags & 1) */
+	int16_t subdir;    /* half-pixel direction 0..7, 8 = none */
+	int16_t flags;     /* 1 = texture gate passed (searched), 2 = accepted (best_sad < value threshold) */
+	uint32_t best_sad; /* 0xFFFFFFFF when not searched */
+	uint32_t texture;  /* compute_diff */
+} aof_dense_block;
+
+typedef struct aof_sad_dense aof_sad_dense;
+
+int aof_sad_dense_create(const aof_dense_params *p, int device, aof_sad_dense **out);
+void aof_sad_dense_destroy(aof_sad_dense *h);
+/* lattice: nbx x nby blocks, block (i, j) has its origin at (x0 + 8 i, y0 + 8 j) */
+int aof_sad_dense_grid(const aof_sad_dense *h, int *nbx, int *nby, int *x0, int *y0);
+/* n_pairs frame pairs in HOST memory -> field[n_pairs * nby * nbx], synchronous */
+int aof_sad_dense_compute(aof_sad_dense *h, const uint8_t *prev, const uint8_t *cur, int n_pairs, aof_dense_block *field);
+/* DEVICE pointers (4-byte aligned), asynchronous on cuda_stream */
+int aof_sad_dense_compute_device(aof_sad_dense *h, const uint8_t *d_prev, const uint8_t *d_cur, int n_pairs,
+				 aof_dense_block *d_field, void *cuda_stream);
+
 /* optional per-kernel timing (CUDA events around every launch of this library; off by default).
  * aof_timing_read(k, ...) for k in [0, aof_timing_kernels()) waits for the recorded launches and
  * returns the kernel's name, its summed device time and its launch count since the last reset. */

@@ -56,6 +56,10 @@ class Port:
         L.orc_compute_flow_batch.restype = None
         L.orc_compute_flow_batch.argtypes = [u8p, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                              f32p, f32p, i32p]
+        L.orc_dense_grid.restype = None
+        L.orc_dense_grid.argtypes = [C.c_int] * 3 + [i32p] * 4
+        L.orc_dense_field.restype = None
+        L.orc_dense_field.argtypes = [u8p, u8p, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]
         L.orc_px4_new.restype = C.c_void_p
         L.orc_px4_new.argtypes = [C.c_float, C.c_float] + [C.c_int] * 6
         L.orc_px4_free.argtypes = [C.c_void_p]
@@ -195,3 +199,19 @@ class _RefPX4:
         if getattr(self, "h", None):
             self.L.ref_px4_free(self.h)
             self.h = None
+
+
+dense_block_dtype = np.dtype([("dx", np.int16), ("dy", np.int16), ("subdir", np.int16), ("flags", np.int16),
+                              ("best_sad", np.uint32), ("texture", np.uint32)])
+
+
+def dense_field(port, prev, cur, search=8, feat_thr=30, val_thr=3000):
+    """oracle dense field of one frame pair -> array [nby, nbx] of dense_block_dtype"""
+    prev = np.ascontiguousarray(prev, np.uint8); cur = np.ascontiguousarray(cur, np.uint8)
+    h, w = prev.shape
+    g = [C.c_int() for _ in range(4)]
+    port.L.orc_dense_grid(w, h, search, *[C.byref(x) for x in g])
+    nbx, nby = g[2].value, g[3].value
+    out = np.zeros((nby, nbx), dense_block_dtype)
+    port.L.orc_dense_field(_p(prev, u8p), _p(cur, u8p), w, h, search, feat_thr, val_thr, C.c_void_p(out.ctypes.data))
+    return out

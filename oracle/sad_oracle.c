@@ -263,3 +263,44 @@ void orc_compute_flow_batch(const uint8_t *prev, const uint8_t *cur, int n, int 
 		quality[i] = orc_compute_flow(prev + i * fs, cur + i * fs, width, search, feat_thr, val_thr,
 					      &flow_x[i], &flow_y[i], NULL);
 }
+
+/* ---- dense field (BASELINE config 4): the same three primitives on every 8x8 block of the 8-px lattice
+ * whose search window + 1 px lies inside the image; 32-bit offsets.  out[nby * nbx] records of 16 bytes:
+ * int16 dx, dy, subdir, flags (1 searched, 2 accepted), uint32 best_sad, uint32 texture. */
+typedef struct { int16_t dx, dy, subdir, flags; uint32_t best_sad, texture; } orc_dense_block;
+
+void orc_dense_grid(int w, int h, int search, int *i_lo, int *j_lo, int *nbx, int *nby)
+{
+	*i_lo = (search + 1 + 7) / 8; *j_lo = *i_lo;
+	*nbx = (w - search - 9) / 8 - *i_lo + 1;
+	*nby = (h - search - 9) / 8 - *j_lo + 1;
+}
+
+void orc_dense_field(const uint8_t *prev, const uint8_t *cur, int w, int h, int search, uint32_t feat_thr, uint32_t val_thr,
+		     orc_dense_block *out)
+{
+	int i_lo, j_lo, nbx, nby;
+	orc_dense_grid(w, h, search, &i_lo, &j_lo, &nbx, &nby);
+	for (int bj = 0; bj < nby; bj++)
+		for (int bi = 0; bi < nbx; bi++) {
+			const int x = 8 * (i_lo + bi), y = 8 * (j_lo + bj);
+			orc_dense_block o = {0, 0, 8, 0, 0xFFFFFFFFu, 0};
+			o.texture = orc_block_texture(prev, x, y, w);
+			if (o.texture >= feat_thr) {
+				o.flags = 1;
+				for (int jj = -search; jj <= search; jj++)
+					for (int ii = -search; ii <= search; ii++) {
+						const uint32_t d = orc_sad8x8(prev, cur, x, y, x + ii, y + jj, w);
+						if (d < o.best_sad) { o.best_sad = d; o.dx = (int16_t)ii; o.dy = (int16_t)jj; }
+					}
+				if (o.best_sad < val_thr) {
+					uint32_t acc[8], best = o.best_sad;
+					o.flags |= 2;
+					orc_subpixel(prev, cur, x, y, x + o.dx, y + o.dy, w, acc);
+					for (int k = 0; k < 8; k++)
+						if (acc[k] < best) { best = acc[k]; o.subdir = (int16_t)k; }
+				}
+			}
+			out[bj * nbx + bi] = o;
+		}
+}
