@@ -103,6 +103,11 @@ def lib():
     L.aof_sad_dense_grid.argtypes = [vp, ip, ip, ip, ip]
     L.aof_sad_dense_compute.argtypes = [vp, u8p, u8p, C.c_int, vp]
     L.aof_sad_dense_compute_device.argtypes = [vp, u8p, u8p, C.c_int, vp, vp]
+    L.aof_gftt_create.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.aof_gftt_destroy.argtypes = [vp]
+    L.aof_gftt_destroy.restype = None
+    L.aof_gftt_min_eig.argtypes = [vp, u8p, C.c_int, vp]
+    L.aof_gftt_detect.argtypes = [vp, u8p, C.c_int, C.c_int, C.c_double, C.c_double, vp, vp]
     _lib = L
     return L
 
@@ -306,3 +311,34 @@ class SadDense:
     def compute_device(self, d_prev, d_cur, n, d_field, stream=0):
         check(lib().aof_sad_dense_compute_device(self.handle, d_prev, d_cur, n, d_field, stream or None),
               "aof_sad_dense_compute_device")
+
+
+class Gftt:
+    """cv::cornerMinEigenVal / cv::goodFeaturesToTrack on the GPU (aof_gftt_*)."""
+
+    def __init__(self, width, height, device=0):
+        self.w, self.h = width, height
+        self.handle = C.c_void_p()
+        check(lib().aof_gftt_create(width, height, device, C.byref(self.handle)), "aof_gftt_create")
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib().aof_gftt_destroy(self.handle)
+            self.handle = None
+
+    __del__ = close
+
+    def min_eig(self, imgs):
+        imgs = np.ascontiguousarray(imgs, np.uint8).reshape(-1, self.h, self.w)
+        out = np.zeros(imgs.shape, np.float32)
+        check(lib().aof_gftt_min_eig(self.handle, _ptr(imgs), len(imgs), _ptr(out)), "aof_gftt_min_eig")
+        return out
+
+    def detect(self, imgs, max_corners, quality, min_distance):
+        imgs = np.ascontiguousarray(imgs, np.uint8).reshape(-1, self.h, self.w)
+        n = len(imgs)
+        xy = np.zeros((n, max_corners, 2), np.float32)
+        cnt = np.zeros(n, np.int32)
+        check(lib().aof_gftt_detect(self.handle, _ptr(imgs), n, max_corners, quality, min_distance, _ptr(xy), _ptr(cnt)),
+              "aof_gftt_detect")
+        return [xy[i, :cnt[i]] for i in range(n)]

@@ -228,6 +228,20 @@ int aof_sad_dense_compute(aof_sad_dense *h, const uint8_t *prev, const uint8_t *
 int aof_sad_dense_compute_device(aof_sad_dense *h, const uint8_t *d_prev, const uint8_t *d_cur, int n_pairs,
 				 aof_dense_block *d_field, void *cuda_stream);
 
+/* ------------------------------------------------- Shi-Tomasi / goodFeaturesToTrack */
+
+/* The corner selector north_star names (the reference selects with FAST):
+ * cv::cornerMinEigenVal(img, blockSize 3, Sobel 3) and cv::goodFeaturesToTrack(img, maxCorners,
+ * qualityLevel, minDistance) on n frames of width x height (HOST pointers, synchronous). */
+typedef struct aof_gftt aof_gftt;
+int aof_gftt_create(int width, int height, int device, aof_gftt **out);
+void aof_gftt_destroy(aof_gftt *g);
+/* eig[n * height * width] */
+int aof_gftt_min_eig(aof_gftt *g, const uint8_t *imgs, int n, float *eig);
+/* xy[n * max_corners * 2] (x, y), counts[n]; corners in cv's order (response desc, address desc) */
+int aof_gftt_detect(aof_gftt *g, const uint8_t *imgs, int n, int max_corners, double quality_level, double min_distance,
+		    float *xy, int *counts);
+
 /* optional per-kernel timing (CUDA events around every launch of this library; off by default).
  * aof_timing_read(k, ...) for k in [0, aof_timing_kernels()) waits for the recorded launches and
  * returns the kernel's name, its summed device time and its launch count since the last reset. */

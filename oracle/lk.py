@@ -51,10 +51,10 @@ def lib():
     L.olk_set_camera_distortion.restype = None
     L.olk_undistort.argtypes = [f32p, f32p, f32p]
     L.olk_undistort.restype = None
-    if hasattr(L, "olk_min_eig"):
-        L.olk_min_eig.argtypes = [u8p, C.c_int, C.c_int, f32p]
-        L.olk_min_eig.restype = None
-        L.olk_gftt.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, f32p]
+    L.olk_min_eig.argtypes = [u8p, C.c_int, C.c_int, f32p]
+    L.olk_min_eig.restype = None
+    L.olk_gftt.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, f32p]
+    L.olk_gftt.restype = C.c_int
     _L = L
     return L
 
@@ -172,3 +172,21 @@ def undistort(cam, dc, pts):
     for i in range(len(out)):
         lib().olk_undistort(_p(cam, f32p), _p(dc, f32p), _p(out[i:i + 1], f32p))
     return out
+
+
+def min_eig(img):
+    """cv::cornerMinEigenVal(img, 3, 3)"""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    out = np.zeros((h, w), np.float32)
+    lib().olk_min_eig(_p(img, u8p), w, h, _p(out, f32p))
+    return out
+
+
+def gftt(img, max_corners, quality, min_distance):
+    """cv::goodFeaturesToTrack(img, max_corners, quality, min_distance) -> [n, 2] (x, y)"""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    xy = np.zeros((max(1, max_corners), 2), np.float32)
+    n = lib().olk_gftt(_p(img, u8p), w, h, max_corners, quality, min_distance, _p(xy, f32p))
+    return xy[:n].copy()

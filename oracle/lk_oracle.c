@@ -627,3 +627,93 @@ void olk_get_state(const olk_tracker *t, int *update_vec, float *feat_cur, float
 	diag[0] = t->last_fast_bins; diag[1] = t->last_inliers; diag[2] = t->last_active; diag[3] = t->n_prev_corners;
 	memcpy(&diag[4], &t->last_px_x, 4); memcpy(&diag[5], &t->last_px_y, 4);
 }
+
+/* ---------------------------------------------------------------- Shi-Tomasi / goodFeaturesToTrack (App. A.6)
+ * named by north_star, not called by the reference.  Restates cv::cornerMinEigenVal(blockSize 3, Sobel 3) and
+ * cv::goodFeaturesToTrack as cv2 4.13 evaluates them for u8 input:
+ *   Dx = sepFilter(row [-1 0 1], column [s 2s s]),  Dy = sepFilter(row [s 2s s], column [-1 0 1]),  s = (float)(1/3060),
+ *   both f32 with BORDER_REFLECT_101;  cov = (DxDx, DxDy, DyDy) box-summed 3x3 in double (reflect-101), cast to f32;
+ *   lambda_min = (a/2 + c/2) - sqrt((a/2 - c/2)^2 + b^2).
+ * cv2's vectorised column filter may fuse multiply-adds, so parity with cv2 is a tolerance (tests/test_oracle_lk.py). */
+static void sobel_dxdy(const u8 *img, int w, int h, int x, int y, float *dx, float *dy)
+{
+	const float s = (float)(1. / 3060.), s2 = 2.f * s;
+	float rx[3], ry[3]; /* row-filtered values of rows y-1, y, y+1 */
+	for (int j = 0; j < 3; j++) {
+		const u8 *r = img + (size_t)reflect101(y + j - 1, h) * w;
+		const int a = r[reflect101(x - 1, w)], b = r[x], c = r[reflect101(x + 1, w)];
+		rx[j] = (float)(c - a);
+		ry[j] = (float)(a + c) * s + (float)b * s2;
+	}
+	*dx = (rx[0] + rx[2]) * s + rx[1] * s2;
+	*dy = ry[2] - ry[0];
+}
+
+void olk_min_eig(const u8 *img, int w, int h, float *eig)
+{
+	float *cov = (float *)malloc(sizeof(float) * 3 * (size_t)w * h);
+	for (int y = 0; y < h; y++)
+		for (int x = 0; x < w; x++) {
+			float dx, dy;
+			sobel_dxdy(img, w, h, x, y, &dx, &dy);
+			float *c = cov + 3 * ((size_t)y * w + x);
+			c[0] = dx * dx; c[1] = dx * dy; c[2] = dy * dy;
+		}
+	for (int y = 0; y < h; y++)
+		for (int x = 0; x < w; x++) {
+			double s[3] = {0, 0, 0};
+			for (int j = -1; j <= 1; j++)
+				for (int i = -1; i <= 1; i++) {
+					const float *c = cov + 3 * ((size_t)reflect101(y + j, h) * w + reflect101(x + i, w));
+					s[0] += c[0]; s[1] += c[1]; s[2] += c[2];
+				}
+			const float a = (float)s[0] * 0.5f, b = (float)s[1], c = (float)s[2] * 0.5f;
+			eig[(size_t)y * w + x] = (a + c) - sqrtf((a - c) * (a - c) + b * b);
+		}
+	free(cov);
+}
+
+typedef struct { float v; int idx; } gftt_cand;
+static int gftt_cmp(const void *a, const void *b)
+{
+	const gftt_cand *p = (const gftt_cand *)a, *q = (const gftt_cand *)b;
+	if (p->v != q->v) return p->v > q->v ? -1 : 1;
+	return q->idx - p->idx; /* ties: higher address first */
+}
+
+/* -> number of corners written to xy[2 * max_corners] */
+int olk_gftt(const u8 *img, int w, int h, int max_corners, double quality, double min_dist, float *xy)
+{
+	float *eig = (float *)malloc(sizeof(float) * (size_t)w * h);
+	olk_min_eig(img, w, h, eig);
+	float mx = eig[0];
+	for (size_t i = 1; i < (size_t)w * h; i++) if (eig[i] > mx) mx = eig[i];
+	const float thr = (float)((double)mx * quality);
+	for (size_t i = 0; i < (size_t)w * h; i++) if (!(eig[i] > thr)) eig[i] = 0.f;
+	gftt_cand *cand = (gftt_cand *)malloc(sizeof(gftt_cand) * (size_t)w * h);
+	int nc = 0;
+	for (int y = 1; y < h - 1; y++)
+		for (int x = 1; x < w - 1; x++) {
+			const float v = eig[(size_t)y * w + x];
+			if (v == 0.f) continue;
+			float m = v;
+			for (int j = -1; j <= 1; j++)
+				for (int i = -1; i <= 1; i++) { const float u = eig[(size_t)(y + j) * w + x + i]; if (u > m) m = u; }
+			if (v == m) { cand[nc].v = v; cand[nc].idx = y * w + x; nc++; }
+		}
+	qsort(cand, nc, sizeof(gftt_cand), gftt_cmp);
+	int n = 0;
+	const float md2 = (float)(min_dist * min_dist);
+	for (int i = 0; i < nc && (max_corners <= 0 || n < max_corners); i++) {
+		const int x = cand[i].idx % w, y = cand[i].idx / w;
+		int ok = 1;
+		if (min_dist >= 1)
+			for (int j = 0; j < n && ok; j++) {
+				const float dx = (float)x - xy[2 * j], dy = (float)y - xy[2 * j + 1];
+				if (dx * dx + dy * dy < md2) ok = 0;
+			}
+		if (ok) { xy[2 * n] = (float)x; xy[2 * n + 1] = (float)y; n++; }
+	}
+	free(cand); free(eig);
+	return n;
+}
