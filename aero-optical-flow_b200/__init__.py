@@ -6,5 +6,5 @@ include/aof.h) and cpp/ (header-compatible C++ shims of the reference classes).
 makes deterministic test frames.  The directory name is not a Python identifier:
 load it with __graft_entry__.load_package() (module name `aof_b200`).
 """
-from . import capi, synth  # noqa: F401
+from . import capi, sharding, synth  # noqa: F401
 from .capi import AofError, Gftt, LkFlow, Px4Flow, SadDense, lib  # noqa: F401
