@@ -134,6 +134,9 @@ struct LkCamera {
 
 cudaError_t lk_pyr_down_launch(const uint8_t *src, uint8_t *dst, int sw, int sh, int n, cudaStream_t st);
 cudaError_t lk_pyr_fused_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1, uint8_t *l2, uint8_t *l3, int n, cudaStream_t st);
+// streaming 3-level pyramid (lk_pyr_stream.cu); needs W % 32 == 0, H % 8 == 0, an 8-byte aligned batch
+bool lk_pyr_stream_supported(const LkGeom &g, const uint8_t *l0);
+cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1, uint8_t *l2, uint8_t *l3, int n, cudaStream_t st);
 cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
 				   int have_prev, cudaStream_t st);
 cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map,

@@ -47,6 +47,7 @@ static LkPyr pyr_of(const aof_lk *h, int slot)
 // levels 1..top of n frames whose level 0 is at l0; level blocks at upper + off[l]
 static cudaError_t build_upper(const LkGeom &g, const uint8_t *l0, uint8_t *upper, const size_t *off, int n, cudaStream_t st)
 {
+	if (lk_pyr_stream_supported(g, l0)) return lk_pyr_stream_launch(g, l0, upper + off[1], upper + off[2], upper + off[3], n, st);
 	if (g.top == 3) return lk_pyr_fused_launch(g, l0, upper + off[1], upper + off[2], upper + off[3], n, st);
 	for (int l = 1; l <= g.top; l++) {
 		const uint8_t *src = l == 1 ? l0 : upper + off[l - 1];

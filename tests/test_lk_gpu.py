@@ -34,6 +34,24 @@ def test_pyramid_bit_exact(pkg, w, h):
     f.close()
 
 
+@pytest.mark.parametrize("w,h,bands", [(640, 480, 1), (640, 480, 2), (640, 480, 7), (640, 480, 60), (1280, 720, 3), (96, 80, 1),
+                                       (256, 88, 2), (288, 80, 1), (544, 128, 4)])
+def test_pyramid_stream_kernel_bands(pkg, w, h, bands, monkeypatch):
+    """the streaming 3-level kernel (W % 32 == 0, H % 8 == 0) with forced band counts: every strip / band seam and
+    every per-level reflect-101 border against the oracle"""
+    monkeypatch.setenv("AOF_PYR_BANDS", str(bands))
+    rng = np.random.default_rng(w * 7 + h + bands)
+    imgs = rng.integers(0, 256, (2, h, w), dtype=np.uint8)
+    f = pkg.LkFlow(FX, FY, -1, w, h)
+    levels = f.pyramid(imgs)
+    assert len(levels) == 4
+    for i in range(len(imgs)):
+        ref = olk.build_pyramid(imgs[i])
+        for l in range(4):
+            assert np.array_equal(levels[l][i], ref[l]), (i, l, np.argwhere(levels[l][i] != ref[l])[:5])
+    f.close()
+
+
 def test_pyramid_golden(pkg):
     for case in GOLD["pyr"]:
         img = pkg.synth.lk_sequence(1, case["w"], case["h"], 1, 1, seed=case["seed"])[0]
