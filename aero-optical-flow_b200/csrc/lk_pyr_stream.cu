@@ -30,7 +30,7 @@
 namespace aof {
 
 constexpr int PS_MAX_STRIPS = 8;
-constexpr int PS_WARPS = 4;
+constexpr int PS_WARPS = 1; // one warp per CTA: blockIdx-derived row bounds are provably warp-uniform, so SHFL needs no WARPSYNC
 
 struct PsStrips {
 	int n;
@@ -213,6 +213,192 @@ lk_pyr_stream_kernel(LkGeom g, const uint8_t *__restrict__ l0, uint8_t *__restri
 	}
 }
 
+// ---------------------------------------------------------------------------
+// Same algorithm for H % 16 == 0, with the row loop unrolled by 8 level-1 rows (= 4 level-2 rows
+// = 2 level-3 rows) starting on a multiple of 8: which rows emit into which level is then static
+// and nothing in the loop is conditional except the stores (outputs of a filter that has not yet
+// seen its five rows are computed and dropped).  Instead of a ring of rows each level keeps two
+// partial sums of the vertical filter:
+//     after an even row c:  P = a + 4 b + 6 c   (the output centred on c, still missing 4 d + e),  Q = c
+//     after an odd row d:   P += 4 d,  Q = c + 4 d   (the head of the NEXT output)
+//     next even row e:      out = P + e;  P = Q + 6 e;  Q = e
+// Top border (rows -2, -1 mirror rows 2, 1): the first output is 6 r0 + 8 r1 + 2 r2, i.e. the same
+// updates with the multipliers of d and e doubled (P starts from Q = 0).  Bottom border of an
+// even-sized level (row H mirrors H - 2 = c): out = P + c = P + Q - 4 d when the last (odd) row arrives.
+struct PsAcc {
+	Row4 P, Q;
+};
+
+// 4 instructions per register and row pair (three IMAD and one IADD)
+#define PS_ODD1(P, Q, d, md) { P = (d) * (md) + P; Q = (d) * 4u + Q; }
+#define PS_EVEN1(P, Q, e, me, out) { out = (e) * (me) + P; P = (e) * 6u + Q; Q = (e); }
+
+__device__ __forceinline__ void ps_odd(PsAcc &s, const Row4 &d, uint32_t md)
+{
+	PS_ODD1(s.P.e01, s.Q.e01, d.e01, md) PS_ODD1(s.P.e23, s.Q.e23, d.e23, md)
+	PS_ODD1(s.P.o01, s.Q.o01, d.o01, md) PS_ODD1(s.P.o23, s.Q.o23, d.o23, md)
+}
+
+__device__ __forceinline__ Row4 ps_even(PsAcc &s, const Row4 &e, uint32_t me)
+{
+	Row4 v;
+	PS_EVEN1(s.P.e01, s.Q.e01, e.e01, me, v.e01) PS_EVEN1(s.P.e23, s.Q.e23, e.e23, me, v.e23)
+	PS_EVEN1(s.P.o01, s.Q.o01, e.o01, me, v.o01) PS_EVEN1(s.P.o23, s.Q.o23, e.o23, me, v.o23)
+	return v;
+}
+
+// bottom border: P + Q - 4 d
+__device__ __forceinline__ Row4 ps_bottom(const PsAcc &s, const Row4 &d)
+{
+	Row4 v;
+	v.e01 = s.P.e01 + s.Q.e01 - 4u * d.e01; v.e23 = s.P.e23 + s.Q.e23 - 4u * d.e23;
+	v.o01 = s.P.o01 + s.Q.o01 - 4u * d.o01; v.o23 = s.P.o23 + s.Q.o23 - 4u * d.o23;
+	return v;
+}
+
+// ps_horz with the border substitutions folded into the PRMT selectors (per-lane constants):
+//   A  = (V-2, V0): 0x5432 from (le, e01);  left border  (V2, V0) = 0x5476 (e01 only)
+//   B  = (V-1, V1): 0x5432 from (lo, o01);  left border  (V1, V1) = 0x5454
+//   Ep = (V6, V8):  0x5432 from (e23, re);  right border (V6, V6) = 0x3232
+struct PsSel {
+	uint32_t a, b, ep;
+};
+
+__device__ __forceinline__ PsSel ps_make_sel(bool left, bool right)
+{
+	PsSel s;
+	s.a = left ? 0x5476u : 0x5432u; s.b = left ? 0x5454u : 0x5432u; s.ep = right ? 0x3232u : 0x5432u;
+	return s;
+}
+
+__device__ __forceinline__ uint32_t ps_horz_sel(const Row4 &v, const PsSel &s)
+{
+	const uint32_t le = __shfl_up_sync(0xFFFFFFFFu, v.e23, 1);
+	const uint32_t lo = __shfl_up_sync(0xFFFFFFFFu, v.o23, 1);
+	const uint32_t re = __shfl_down_sync(0xFFFFFFFFu, v.e01, 1);
+	const uint32_t A = __byte_perm(le, v.e01, s.a);
+	const uint32_t B = __byte_perm(lo, v.o01, s.b);
+	const uint32_t E = __byte_perm(v.e01, v.e23, 0x5432);
+	const uint32_t Bp = __byte_perm(v.o01, v.o23, 0x5432);
+	const uint32_t Ep = __byte_perm(v.e23, re, s.ep);
+	const uint32_t r01 = A + E + 0x00800080u + 4u * (B + v.o01) + 6u * v.e01;
+	const uint32_t r23 = E + Ep + 0x00800080u + 4u * (Bp + v.o23) + 6u * v.e23;
+	return __byte_perm(r01, r23, 0x7531);
+}
+
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(PS_WARPS * 32, MIN_CTAS)
+lk_pyr_stream16_kernel(LkGeom g, const uint8_t *__restrict__ l0, uint8_t *__restrict__ l1, uint8_t *__restrict__ l2,
+		       uint8_t *__restrict__ l3, PsStrips ss, int bands, int band_rows, int n_tasks)
+{
+	const int lane = threadIdx.x & 31;
+	const int task = blockIdx.x * PS_WARPS + (threadIdx.x >> 5);
+	if (task >= n_tasks) return;
+	const int strip = task % ss.n;
+	const int band = (task / ss.n) % bands;
+	const size_t frame = (size_t)(task / (ss.n * bands));
+	const int W0 = g.w[0], H0 = g.h[0], W1 = g.w[1], H1 = g.h[1], W2 = g.w[2], H2 = g.h[2], W3 = g.w[3], H3 = g.h[3];
+	const int R0 = band * band_rows, R1 = min(H3, R0 + band_rows);
+	if (R0 >= H3) return;
+	const int s0 = ss.s0[strip], oa = ss.oa[strip], ob = ss.ob[strip];
+	const int c0 = s0 + 8 * lane;
+	const bool in0 = c0 < W0, left0 = c0 == 0, right0 = c0 + 8 == W0;
+	const int x1 = (s0 >> 1) + 4 * lane;
+	const bool own1 = in0 && x1 >= 4 * oa && x1 < 4 * ob;
+	const int c1 = (s0 >> 1) + 8 * lane;
+	const bool left1 = lane < 16 && c1 == 0, right1 = lane < 16 && c1 + 8 == W1;
+	const int x2 = (s0 >> 2) + 4 * lane;
+	const bool own2 = lane < 16 && x2 >= 2 * oa && x2 < 2 * ob;
+	const int c2 = (s0 >> 2) + 8 * lane;
+	const bool left2 = lane < 8 && c2 == 0, right2 = lane < 8 && c2 + 8 == W2;
+	const int x3 = (s0 >> 3) + 4 * lane;
+	const bool own3 = lane < 8 && x3 >= oa && x3 < ob;
+	const PsSel sel0 = ps_make_sel(left0, right0), sel1 = ps_make_sel(left1, right1), sel2 = ps_make_sel(left2, right2);
+
+	// level-1 rows [Ya, Yb): the band's own rows plus the cone, widened to whole groups of 8
+	const int Ya = max(0, 4 * R0 - 6) & ~7;
+	const int Yb = min(H1, (4 * R1 + 3 + 7) & ~7);
+
+	// lanes right of the image read column 0 (their results are never used): no predicate on the loads
+	const uint8_t *img = l0 + frame * (size_t)W0 * H0 + (in0 ? c0 : 0);
+	// running store pointers: row Ya of level 1, the level-2 / level-3 rows the first group emits
+	uint8_t *o1 = l1 + frame * (size_t)W1 * H1 + x1 + (size_t)Ya * W1;
+	uint8_t *o2 = l2 + frame * (size_t)W2 * H2 + x2 + ((ptrdiff_t)(Ya >> 1) - 1) * W2;
+	uint8_t *o3 = l3 + frame * (size_t)W3 * H3 + x3 + ((ptrdiff_t)(Ya >> 2) - 1) * W3;
+
+	// byte offset of a row inside the frame.  Odd rows are clamped to the last row (only ever hit by the
+	// prefetch running past the image); even rows to row H0 - 2, which is exactly the mirror of row H0.
+	const uint32_t off_odd_max = (uint32_t)(H0 - 1) * W0, off_even_max = (uint32_t)(H0 - 2) * W0;
+	auto load_odd = [&](uint32_t off) -> uint2 { return __ldg(reinterpret_cast<const uint2 *>(img + min(off, off_odd_max))); };
+	auto load_even = [&](uint32_t off) -> uint2 { return __ldg(reinterpret_cast<const uint2 *>(img + min(off, off_even_max))); };
+	PsAcc f0, f1 = {}, f2 = {};
+	uint32_t ro = (uint32_t)(2 * Ya) * W0; // row 2 Ya
+	{
+		Row4 a = {}, b = {};
+		if (Ya > 0) {
+			const uint2 ra = load_even(ro - 2 * W0), rb = load_odd(ro - W0);
+			a = ps_split(ra.x, ra.y); b = ps_split(rb.x, rb.y);
+		}
+		const uint2 rc = load_even(ro);
+		const Row4 c = ps_split(rc.x, rc.y);
+		f0.P.e01 = a.e01 + 4u * b.e01 + 6u * c.e01; f0.P.e23 = a.e23 + 4u * b.e23 + 6u * c.e23;
+		f0.P.o01 = a.o01 + 4u * b.o01 + 6u * c.o01; f0.P.o23 = a.o23 + 4u * b.o23 + 6u * c.o23;
+		f0.Q = c;
+	}
+	// rows 2 Y + 1, 2 Y + 2 of two iterations in flight
+	ro += W0;
+	uint2 qa0 = load_odd(ro), qb0 = load_even(ro + W0);
+	ro += 2 * W0;
+	uint2 qa1 = load_odd(ro), qb1 = load_even(ro + W0);
+	ro += 2 * W0;
+	const int src0 = (2 * lane) & 31, src1 = (2 * lane + 1) & 31;
+
+	for (int Yg = Ya; Yg < Yb; Yg += 8) {
+		const bool first = Yg == 0;
+		const uint32_t m8 = first ? 8u : 4u, m2 = first ? 2u : 1u;
+#pragma unroll
+		for (int k = 0; k < 8; k++) {
+			const int Y = Yg + k;
+			const uint2 ca = qa0, cb = qb0;
+			qa0 = qa1; qb0 = qb1;
+			qa1 = load_odd(ro); qb1 = load_even(ro + W0);
+			ro += 2 * W0;
+			// ---- level 0 -> level-1 row Y
+			ps_odd(f0, ps_split(ca.x, ca.y), k == 0 ? m8 : 4u);
+			const uint32_t w1 = ps_horz_sel(ps_even(f0, ps_split(cb.x, cb.y), k == 0 ? m2 : 1u), sel0);
+			if (own1 && Y >= 4 * R0 && Y < 4 * R1) *reinterpret_cast<uint32_t *>(o1) = w1;
+			o1 += W1;
+			const Row4 n1 = ps_split(__shfl_sync(0xFFFFFFFFu, w1, src0), __shfl_sync(0xFFFFFFFFu, w1, src1));
+			if (k & 1) { // static: odd level-1 row
+				ps_odd(f1, n1, k == 1 ? m8 : 4u);
+				if (k == 7 && Y == H1 - 1) { // bottom of the image: level-2 row H2 - 1, then level-3 row H3 - 1
+					const uint32_t wb2 = ps_horz_sel(ps_bottom(f1, n1), sel1);
+					if (own2 && H2 - 1 < 2 * R1) *reinterpret_cast<uint32_t *>(o2) = wb2;
+					const Row4 nb = ps_split(__shfl_sync(0xFFFFFFFFu, wb2, src0), __shfl_sync(0xFFFFFFFFu, wb2, src1));
+					ps_odd(f2, nb, 4u);
+					const uint32_t wb3 = ps_horz_sel(ps_bottom(f2, nb), sel2);
+					if (own3 && H3 - 1 < R1) *reinterpret_cast<uint32_t *>(o3) = wb3;
+				}
+				continue;
+			}
+			// ---- level-1 row Y (even) completes level-2 row Z = (Y - 2) / 2
+			const int Z = (Y - 2) >> 1;
+			const uint32_t w2 = ps_horz_sel(ps_even(f1, n1, k == 2 ? m2 : 1u), sel1);
+			if (own2 && Z >= 2 * R0 && Z < 2 * R1) *reinterpret_cast<uint32_t *>(o2) = w2;
+			o2 += W2;
+			const Row4 n2 = ps_split(__shfl_sync(0xFFFFFFFFu, w2, src0), __shfl_sync(0xFFFFFFFFu, w2, src1));
+			if ((k & 3) != 2) { // static: Z odd.  (Z = -1 of the first group does not exist: the filter must start from 0)
+				if (k == 4 || !first) ps_odd(f2, n2, k == 4 ? m8 : 4u);
+				continue;
+			}
+			const int R = (Z - 2) >> 1;
+			const uint32_t w3 = ps_horz_sel(ps_even(f2, n2, k == 6 ? m2 : 1u), sel2);
+			if (own3 && R >= R0 && R < R1) *reinterpret_cast<uint32_t *>(o3) = w3;
+			o3 += W3;
+		}
+	}
+}
+
 // ---- host side -------------------------------------------------------------
 // Column strips: the first starts at column 0 and owns level-3 columns [0, 28); every further strip
 // owning from `oa` starts 32 level-0 columns (= the 14-px cone rounded up to the lane grid of level 2)
@@ -271,9 +457,17 @@ cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1
 	const int band_rows = (g.h[3] + bands - 1) / bands;
 	const long long tasks = (long long)ss.n * bands * n;
 	if (tasks > 0x7FFFFFFFLL) return cudaErrorInvalidValue;
+	const unsigned blocks = (unsigned)((tasks + PS_WARPS - 1) / PS_WARPS);
+	const char *v1 = getenv("AOF_PYR_V1");
 	KernelTimer kt(KID_LK_PYR_FUSED, st);
-	lk_pyr_stream_kernel<<<(unsigned)((tasks + PS_WARPS - 1) / PS_WARPS), PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands,
-												      band_rows, (int)tasks);
+	const char *occ = getenv("AOF_PYR_OCC");
+	const int o = occ ? atoi(occ) : 16; // measured on B200: 16 CTAs/SM (<= 128 registers) is the fastest
+	if (g.h[0] % 16 == 0 && !(v1 && v1[0] == '1')) {
+		if (o <= 16) lk_pyr_stream16_kernel<16><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+		else if (o <= 20) lk_pyr_stream16_kernel<20><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+		else lk_pyr_stream16_kernel<24><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+	} else
+		lk_pyr_stream_kernel<<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 	count_launch();
 	return cudaGetLastError();
 }
