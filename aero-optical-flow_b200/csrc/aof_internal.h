@@ -141,6 +141,9 @@ cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkP
 				   int have_prev, cudaStream_t st);
 cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map,
 			   cudaStream_t st);
+// banded FAST (lk_fast_band.cu); lk_fast_launch dispatches to it when the shape allows
+bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0);
+cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st);
 cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
 				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
 				      float fy, const LkCamera &cam, cudaStream_t st);

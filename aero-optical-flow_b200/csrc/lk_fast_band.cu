@@ -1,0 +1,235 @@
+// K4b  lk_fast_band: cv::FAST(bin ROI, keypoints, 10, nonmaxSuppression = true) for the bins that
+// need features (external/klt_feature_tracker/src/trackFeatures.cpp:196), one CTA
+// per (stream, bin, band of 38 rows).  Integer-ALU bound: the exact corner response of EVERY pixel
+// is a fixed min / max network (no test-then-score branch; on the LK benchmark texture more than a
+// third of the pixels are corners), two horizontally adjacent pixels per thread in u16x2 lanes.
+//
+//   * FAST runs on the bin as a stand-alone image, so a band needs only rows of its own bin: the
+//     rows [y0 - 4, y0 + 42) are loaded once, each 4-pixel word expanded into the two pair
+//     layouts A = (p[2j], p[2j+1]) and B = (p[2j+1], p[2j+2]) so that every ring tap of a pixel
+//     pair is ONE aligned LDS.32 (ring offsets with odd dx come from A, even dx from B);
+//   * response: with D_k = c + 256 - ring_k per lane, a dark corner of strength s has an arc of
+//     9 with min D - 256 > s, a bright one max D < 256 - s.  The two arcs starting at k and k + 1
+//     (k even) share ring positions k+1 .. k+8, so
+//         max(min9(k), min9(k+1)) = min(min8(k+1), max(D_k, D_k+9))
+//     and the 8 windows min8(odd start) are built from 8 pair-minima: 36 packed min / max per
+//     polarity instead of 40 for the plain sliding window (all VIMNMX / VIMNMX3 .U16x2);
+//   * responses are kept biased, b = max(m, 256 + thr) - (256 + thr) (0 = not a corner, order
+//     preserved), as u16x2 in shared memory; the 3 x 3 non-maximum suppression walks down the
+//     band with the horizontal maxima of the previous / next row carried in registers;
+//   * survivors are collected in shared memory and appended to the bin's list with one global
+//     atomic per CTA.  Entry = score << 24 | bin-local raster index (order in the list is free:
+//     the selection kernel uses the total order score desc, raster asc).
+// Needs bw % 4 == 0, W % 4 == 0, a 4-byte aligned batch and bw <= 512; other shapes use lk_fast_kernel.
+#include <cstdlib>
+
+#include "aof_common.cuh"
+#include "aof_internal.h"
+
+namespace aof {
+
+constexpr int FB_ROWS = 38;             // output rows per band (a 120-row bin has 114 = 3 x 38)
+constexpr int FB_SROWS = FB_ROWS + 2;   // response rows (one above, one below for the suppression)
+constexpr int FB_PROWS = FB_ROWS + 8;   // pixel rows
+constexpr int FB_MAX_GROUPS = 20;       // row groups: thread = (group, pair column); THREADS / (bw / 2) of them
+
+__device__ __forceinline__ uint32_t fb_mn(uint32_t a, uint32_t b) { return __vminu2(a, b); }
+__device__ __forceinline__ uint32_t fb_mx(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
+__device__ __forceinline__ uint32_t fb_mn3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u16x2(a, b, c); }
+__device__ __forceinline__ uint32_t fb_mx3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
+
+// response + 257 per lane of the pixel pair whose centre is B[0][0] (A, B point at the centre row / pair column,
+// P = row pitch in words).  Materialised min3 / max3 only (ptxas 12.9 mis-folds max(m, -x), tools/ptxas_vimnmx3_neg_repro.cu).
+__device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint32_t *B, int P)
+{
+	const uint32_t cb = B[0] + 0x01000100u;
+	uint32_t D[16];
+	D[0] = cb - B[3 * P];       D[1] = cb - A[3 * P + 1];   D[2] = cb - B[2 * P + 1];   D[3] = cb - A[P + 2];
+	D[4] = cb - A[2];           D[5] = cb - A[-P + 2];      D[6] = cb - B[-2 * P + 1];  D[7] = cb - A[-3 * P + 1];
+	D[8] = cb - B[-3 * P];      D[9] = cb - A[-3 * P];      D[10] = cb - B[-2 * P - 1]; D[11] = cb - A[-P - 1];
+	D[12] = cb - A[-1];         D[13] = cb - A[P - 1];      D[14] = cb - B[2 * P - 1];  D[15] = cb - A[3 * P];
+	uint32_t p[8], q[8], Pm[8], Qm[8];
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		p[j] = fb_mn(D[2 * j + 1], D[(2 * j + 2) & 15]);
+		Pm[j] = fb_mx(D[2 * j + 1], D[(2 * j + 2) & 15]);
+	}
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		q[j] = fb_mn(p[j], p[(j + 1) & 7]);
+		Qm[j] = fb_mx(Pm[j], Pm[(j + 1) & 7]);
+	}
+	uint32_t r[8], R[8];
+#pragma unroll
+	for (int i = 0; i < 8; i++) {
+		const uint32_t hi = fb_mx(D[2 * i], D[(2 * i + 9) & 15]);
+		const uint32_t lo = fb_mn(D[2 * i], D[(2 * i + 9) & 15]);
+		r[i] = fb_mn3(q[i], q[(i + 2) & 7], hi);    // best of the dark arcs starting at 2i and 2i + 1
+		R[i] = fb_mx3(Qm[i], Qm[(i + 2) & 7], lo);  // best of the bright arcs
+	}
+	uint32_t dark = fb_mx3(r[0], r[1], r[2]), bright = fb_mn3(R[0], R[1], R[2]);
+	dark = fb_mx3(dark, r[3], r[4]); bright = fb_mn3(bright, R[3], R[4]);
+	dark = fb_mx3(dark, r[5], r[6]); bright = fb_mn3(bright, R[5], R[6]);
+	dark = fb_mx(dark, r[7]); bright = fb_mn(bright, R[7]);
+	return fb_mx(dark, 0x02000200u - bright);
+}
+
+// dynamic shared memory: A[FB_PROWS][P], B[FB_PROWS][P], responses[FB_SROWS][P], survivor list
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P,
+		    int list_cap)
+{
+	extern __shared__ __align__(16) uint32_t fb_smem[];
+	uint32_t *sA = fb_smem;
+	uint32_t *sB = sA + FB_PROWS * P;
+	uint32_t *sS = sB + FB_PROWS * P;
+	uint32_t *sL = sS + FB_SROWS * P;
+	__shared__ int s_n, s_base;
+
+	const size_t stream = blockIdx.y;
+	const int bin = blockIdx.x / bands, band = blockIdx.x - bin * bands;
+	if (!score_map && s.bin_needed[stream * LK_BINS + bin] == 0) return;
+	const int W = g.w[0], H = g.h[0], bw = g.bw, bh = g.bh;
+	const int npc = bw >> 1, nq = bw >> 2;
+	const int c0 = (bin >> 2) * bw, r0 = (bin & 3) * bh;        // bin = x * 4 + y
+	const int y0 = 3 + band * FB_ROWS;                            // first output row of the band (bin coordinates)
+	const int y1 = min(y0 + FB_ROWS, bh - 3);                     // one past the last
+	const int tid = threadIdx.x;
+	if (tid == 0) s_n = 0;
+	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
+
+	// ---- pixel rows y0 - 4 .. y1 + 3 of the bin -> pair layouts (tile row t <-> bin row y0 - 4 + t)
+	const int n_prow = y1 - y0 + 8;
+	for (int i = tid; i < n_prow * nq; i += THREADS) {
+		const int t = i / nq, q = i - t * nq;
+		const int y = y0 - 4 + t;
+		if (y < 0 || y >= bh) continue;                           // rows -1 and bh only feed responses that are not computed
+		const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (size_t)y * W);
+		const uint32_t w0 = __ldg(row + q);
+		const uint32_t w1 = q + 1 < nq ? __ldg(row + q + 1) : 0u; // p[bw] is never used
+		const uint32_t a0 = __byte_perm(w0, 0u, 0x4140), a1 = __byte_perm(w0, 0u, 0x4342);
+		const uint32_t b0 = __byte_perm(w0, 0u, 0x4241), b1 = __byte_perm(__funnelshift_r(w0, w1, 24), 0u, 0x4140);
+		*reinterpret_cast<uint2 *>(sA + t * P + 2 * q) = make_uint2(a0, a1);
+		*reinterpret_cast<uint2 *>(sB + t * P + 2 * q) = make_uint2(b0, b1);
+	}
+	__syncthreads();
+
+	// ---- biased responses of rows y0 - 1 .. y1 (response row sr <-> bin row y0 - 1 + sr, tile row sr + 3)
+	const int grp = tid / npc, j = tid - grp * npc;               // pair column j <-> pixels 2j + 1, 2j + 2
+	const int ngrp = min(THREADS / npc, FB_MAX_GROUPS);
+	const bool col_ok = grp < ngrp && j >= 1 && j <= npc - 3;
+	const int n_srow = y1 - y0 + 2;
+	const uint32_t lim = (256u + (uint32_t)g.fast_thr) * 0x00010001u;
+	if (grp < ngrp) {
+		for (int sr = grp; sr < n_srow; sr += ngrp) {
+			const int y = y0 - 1 + sr;
+			uint32_t b = 0u;
+			if (col_ok && y >= 3 && y < bh - 3) {
+				const uint32_t m = fb_score_pair(sA + (sr + 3) * P + j, sB + (sr + 3) * P + j, P);
+				b = fb_mx(m, lim) - lim;
+			}
+			sS[sr * P + j] = b;
+		}
+	}
+	__syncthreads();
+
+	// ---- 3 x 3 non-maximum suppression, each thread walking down its share of the band's rows
+	if (col_ok) {
+		const int n_out = y1 - y0;
+		const int chunk = (n_out + ngrp - 1) / ngrp;
+		const int ra = 1 + grp * chunk, rb = min(ra + chunk, n_out + 1);   // response rows of this thread's outputs
+		const uint32_t *col = sS + j;
+		auto hmax = [&](int sr, uint32_t &c, uint32_t &side) -> uint32_t {
+			const uint32_t l = col[sr * P - 1], r = col[sr * P + 1];
+			c = col[sr * P];
+			const uint32_t lm = __byte_perm(l, c, 0x5432), rm = __byte_perm(c, r, 0x5432); // (x-1, x), (x+1, x+2)
+			side = fb_mx(lm, rm);
+			return fb_mx3(lm, c, rm);
+		};
+		if (ra < rb) {
+			uint32_t c_prev, c_cur, c_next, side_prev, side_cur, side_next;
+			uint32_t h_prev = hmax(ra - 1, c_prev, side_prev);
+			uint32_t h_cur = hmax(ra, c_cur, side_cur);
+			for (int sr = ra; sr < rb; sr++) {
+				const uint32_t h_next = hmax(sr + 1, c_next, side_next);
+				if (c_cur) {
+					const uint32_t m = fb_mx3(h_prev, h_next, side_cur);
+					const int y = y0 + sr - 1;
+#pragma unroll
+					for (int e = 0; e < 2; e++) {
+						const uint32_t v = (c_cur >> (16 * e)) & 0xFFFFu, mm = (m >> (16 * e)) & 0xFFFFu;
+						if (v > mm) {
+							const int x = 2 * j + 1 + e;
+							const uint32_t score = v + (uint32_t)g.fast_thr - 1u;
+							if (score_map) score_map[stream * (size_t)W * H + (size_t)(r0 + y) * W + c0 + x] = (uint8_t)score;
+							else {
+								const int slot = atomicAdd(&s_n, 1);
+								if (slot < list_cap) sL[slot] = (score << 24) | (uint32_t)(y * bw + x);
+							}
+						}
+					}
+				}
+				h_prev = h_cur; h_cur = h_next; c_cur = c_next; side_cur = side_next;
+			}
+		}
+	}
+	if (score_map) return;
+	__syncthreads();
+	const int n = min(s_n, list_cap);
+	if (tid == 0 && n > 0) s_base = atomicAdd(&s.kp_count[stream * LK_BINS + bin], n);
+	__syncthreads();
+	if (n > 0) {
+		const int base = s_base;
+		uint32_t *list = s.kp + (stream * LK_BINS + bin) * (size_t)g.kp_cap;
+		for (int i = tid; i < n; i += THREADS)
+			if (base + i < g.kp_cap) list[base + i] = sL[i];
+	}
+}
+
+// ---- host side -------------------------------------------------------------
+static size_t fb_smem_bytes(const LkGeom &g, int &P, int &list_cap)
+{
+	const int npc = g.bw / 2;
+	P = npc + 4;
+	list_cap = ((npc + 1) / 2 + 1) * (FB_ROWS / 2 + 1); // strict 3 x 3 maxima cannot be denser
+	return ((size_t)(2 * FB_PROWS + FB_SROWS) * P + list_cap) * sizeof(uint32_t);
+}
+
+bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0)
+{
+	const char *v1 = getenv("AOF_FAST_V1");
+	if (v1 && v1[0] == '1') return false;
+	if (g.bw % 4 || g.w[0] % 4 || (reinterpret_cast<uintptr_t>(l0) & 3) || g.bh < 7 || g.bw < 8 || g.bw > 512) return false;
+	int P, cap;
+	return fb_smem_bytes(g, P, cap) <= 200 * 1024;
+}
+
+template <int THREADS>
+static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
+{
+	int P, cap;
+	const size_t smem = fb_smem_bytes(g, P, cap);
+	static bool attr_set[64] = {};
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev < 64 && !attr_set[dev]) {
+		cudaError_t e = cudaFuncSetAttribute(lk_fast_band_kernel<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+		if (e != cudaSuccess) return e;
+		attr_set[dev] = true;
+	}
+	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
+	dim3 grid(LK_BINS * bands, n);
+	lk_fast_band_kernel<THREADS><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
+	return cudaGetLastError();
+}
+
+cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
+{
+	const int npc = g.bw / 2;
+	if (4 * npc <= 320) return fb_launch<320>(g, l0, s, n, score_map, st);
+	if (4 * npc <= 640) return fb_launch<640>(g, l0, s, n, score_map, st);
+	return fb_launch<1024>(g, l0, s, n, score_map, st);
+}
+
+} // namespace aof

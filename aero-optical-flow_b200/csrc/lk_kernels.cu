@@ -568,6 +568,10 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 	const int tiles_x = (g.bw + FT_TW - 1) / FT_TW, tiles_y = (g.bh + FT_TH - 1) / FT_TH;
 	dim3 grid(tiles_x * tiles_y * LK_BINS, n);
 	KernelTimer kt(KID_LK_FAST, st);
+	if (lk_fast_band_supported(g, l0)) {
+		count_launch();
+		return lk_fast_band_launch(g, l0, s, n, score_map, st);
+	}
 	if (g.w[0] % 16 == 0 && (reinterpret_cast<uintptr_t>(l0) & 3) == 0)
 		lk_fast_kernel<true><<<grid, FT_THREADS, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
 	else

@@ -62,7 +62,7 @@ def test_pyramid_golden(pkg):
         f.close()
 
 
-@pytest.mark.parametrize("w,h", [(640, 480), (128, 128), (64, 64), (100, 76)])
+@pytest.mark.parametrize("w,h", [(640, 480), (128, 128), (64, 64), (100, 76), (1280, 720), (352, 300), (2048, 160)])
 def test_fast_scores_bit_exact(pkg, w, h):
     imgs = np.stack([pkg.synth.lk_sequence(1, w, h, 1, 1, seed=10 + s)[0] for s in range(2)])
     rng = np.random.default_rng(w)
