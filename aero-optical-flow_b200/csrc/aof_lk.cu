@@ -17,7 +17,8 @@ struct aof_lk {
 	aof_lk_params p;
 	int n = 0, device = 0;
 	LkGeom g{};
-	cudaStream_t st = nullptr;
+	cudaStream_t st = nullptr, st_copy = nullptr;
+	cudaEvent_t ev_chunk[8] = {};        // host-batch path: chunk c of the frames has landed
 	size_t lvl_px[LK_MAX_LEVELS] = {};   // pixels of one frame at level l
 	size_t upper_off[LK_MAX_LEVELS] = {}; // offset of the level-l block (l >= 1) inside d_upper[slot]
 	size_t upper_bytes = 0;
@@ -36,12 +37,24 @@ struct aof_lk {
 	aof_lk_raw *h_raw = nullptr, *d_raw = nullptr;
 };
 
-static LkPyr pyr_of(const aof_lk *h, int slot)
+// level base pointers of slot `slot`, seen from stream `first` on
+static LkPyr pyr_of(const aof_lk *h, int slot, size_t first = 0)
 {
 	LkPyr p{};
-	p.lvl[0] = h->l0[slot];
-	for (int l = 1; l <= h->g.top; l++) p.lvl[l] = h->d_upper[slot] + h->upper_off[l];
+	p.lvl[0] = h->l0[slot] + first * h->lvl_px[0];
+	for (int l = 1; l <= h->g.top; l++) p.lvl[l] = h->d_upper[slot] + h->upper_off[l] + first * h->lvl_px[l];
 	return p;
+}
+
+// the per-stream state arrays seen from stream `first` on
+static LkState state_from(const LkState &s, const LkGeom &g, size_t first)
+{
+	LkState v = s;
+	const size_t N = (size_t)g.n_feat;
+	v.prev_corners += first * N; v.prev_status += first * N; v.n_prev_corners += first; v.update_vec += first * N;
+	v.feat_cur += first * N; v.feat_prev += first * N; v.lim += first; v.bin_needed += first * LK_BINS; v.target += first;
+	v.kp_count += first * LK_BINS; v.kp += first * LK_BINS * (size_t)g.kp_cap;
+	return v;
 }
 
 // levels 1..top of n frames whose level 0 is at l0; level blocks at upper + off[l]
@@ -127,7 +140,10 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	h->upper_bytes = off ? off : 256;
 	const size_t nN = (size_t)n_streams * N;
 	cudaError_t e;
+	for (int c = 0; c < 8; c++)
+		if (cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming) != cudaSuccess) h->ev_chunk[c] = nullptr;
 	if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess ||
+	    (e = cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_upper[0], h->upper_bytes)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_upper[1], h->upper_bytes)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.prev_corners, sizeof(float2) * nN)) != cudaSuccess ||
@@ -163,6 +179,9 @@ void aof_lk_destroy(aof_lk *h)
 	cudaFree(h->d_frames[0]); cudaFree(h->d_frames[1]);
 	cudaFreeHost(h->h_stage); cudaFreeHost(h->h_t); cudaFreeHost(h->h_out); cudaFreeHost(h->h_raw);
 	cudaFree(h->d_t); cudaFree(h->d_out); cudaFree(h->d_raw);
+	for (int c = 0; c < 8; c++)
+		if (h->ev_chunk[c]) cudaEventDestroy(h->ev_chunk[c]);
+	if (h->st_copy) cudaStreamDestroy(h->st_copy);
 	if (h->st) cudaStreamDestroy(h->st);
 	delete h;
 }
@@ -178,22 +197,40 @@ int aof_lk_reset(aof_lk *h)
 	return reset_state(h);
 }
 
+// one calcFlow pass over streams [first, first + count) of the batch whose level 0 is h->l0[nxt]
+static int run_range(aof_lk *h, int nxt, const uint32_t *d_t_us, aof_flow_out *d_out, aof_lk_raw *d_raw, int first, int count,
+		     cudaStream_t st)
+{
+	const size_t f = (size_t)first;
+	const LkPyr next = pyr_of(h, nxt, f);
+	const LkPyr prev = h->have_prev ? pyr_of(h, h->cur, f) : next;
+	const LkState sv = state_from(h->s, h->g, f);
+	if (lk_pyr_stream_supported(h->g, next.lvl[0]))
+		AOF_CUDA(lk_pyr_stream_launch(h->g, next.lvl[0], const_cast<uint8_t *>(next.lvl[1]), const_cast<uint8_t *>(next.lvl[2]),
+					      const_cast<uint8_t *>(next.lvl[3]), count, st));
+	else if (h->g.top == 3)
+		AOF_CUDA(lk_pyr_fused_launch(h->g, next.lvl[0], const_cast<uint8_t *>(next.lvl[1]), const_cast<uint8_t *>(next.lvl[2]),
+					     const_cast<uint8_t *>(next.lvl[3]), count, st));
+	else
+		for (int l = 1; l <= h->g.top; l++)
+			AOF_CUDA(lk_pyr_down_launch(next.lvl[l - 1], const_cast<uint8_t *>(next.lvl[l]), h->g.w[l - 1], h->g.h[l - 1], count, st));
+	AOF_CUDA(lk_track_update_launch(h->g, prev, next, sv, count, h->have_prev ? 1 : 0, st));
+	AOF_CUDA(lk_fast_launch(h->g, next.lvl[0], sv, count, nullptr, st));
+	AOF_CUDA(lk_select_epilogue_launch(h->g, sv, d_t_us + f, d_out + f, d_raw ? d_raw + f : nullptr, count,
+					   h->have_feat_prev ? 1 : 0, h->p.output_rate, h->p.confidence_multiplier,
+					   h->p.focal_length_x, h->p.focal_length_y, h->cam, st));
+	return AOF_OK;
+}
+
 int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
 			    aof_lk_raw *d_raw, void *cuda_stream)
 {
 	if (!h || !d_imgs || !d_t_us || !d_out) { set_error("lk calc_flow_device: null argument"); return AOF_ERR_INVALID; }
 	AOF_CUDA(cudaSetDevice(h->device));
-	cudaStream_t st = (cudaStream_t)cuda_stream;
 	const int nxt = h->cur ^ 1;
 	h->l0[nxt] = d_imgs;
-	AOF_CUDA(build_upper(h->g, d_imgs, h->d_upper[nxt], h->upper_off, h->n, st));
-	const LkPyr next = pyr_of(h, nxt);
-	const LkPyr prev = h->have_prev ? pyr_of(h, h->cur) : next;
-	AOF_CUDA(lk_track_update_launch(h->g, prev, next, h->s, h->n, h->have_prev ? 1 : 0, st));
-	AOF_CUDA(lk_fast_launch(h->g, d_imgs, h->s, h->n, nullptr, st));
-	AOF_CUDA(lk_select_epilogue_launch(h->g, h->s, d_t_us, d_out, d_raw, h->n, h->have_feat_prev ? 1 : 0,
-					   h->p.output_rate, h->p.confidence_multiplier, h->p.focal_length_x,
-					   h->p.focal_length_y, h->cam, st));
+	int rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, h->n, (cudaStream_t)cuda_stream);
+	if (rc != AOF_OK) return rc;
 	h->cur = nxt;
 	h->have_prev = h->have_feat_prev = true;
 	return AOF_OK;
@@ -215,20 +252,37 @@ static int ensure_batch_buffers(aof_lk *h)
 	return AOF_OK;
 }
 
+// Host frames in, results out.  The batch is cut into up to 8 chunks of whole streams: chunk c + 1 crosses PCIe on the
+// copy stream while the kernels of chunk c run (streams are independent, so a chunk is a complete calcFlow pass).
 int aof_lk_calc_flow_batch(aof_lk *h, const uint8_t *imgs, const uint32_t *t_us, aof_flow_out *out, aof_lk_raw *raw)
 {
 	if (!h || !imgs || !t_us || !out) { set_error("lk calc_flow_batch: null argument"); return AOF_ERR_INVALID; }
 	AOF_CUDA(cudaSetDevice(h->device));
 	int rc = ensure_batch_buffers(h);
 	if (rc != AOF_OK) return rc;
-	const size_t total = h->lvl_px[0] * h->n;
-	uint8_t *d_cur = h->d_frames[h->cur ^ 1];
-	rc = stage_h2d(d_cur, imgs, total, h->h_stage, h->st);
-	if (rc != AOF_OK) return rc;
+	const int nxt = h->cur ^ 1;
+	uint8_t *d_cur = h->d_frames[nxt];
+	h->l0[nxt] = d_cur;
 	memcpy(h->h_t, t_us, sizeof(uint32_t) * h->n);
 	AOF_CUDA(cudaMemcpyAsync(h->d_t, h->h_t, sizeof(uint32_t) * h->n, cudaMemcpyHostToDevice, h->st));
-	rc = aof_lk_calc_flow_device(h, d_cur, h->d_t, h->d_out, h->d_raw, h->st);
-	if (rc != AOF_OK) return rc;
+	// chunks of >= 16 streams and >= 1 MiB, 8-byte aligned starts (the pyramid kernel loads 8 bytes per lane)
+	int chunks = h->n / 16;
+	if ((size_t)chunks > h->lvl_px[0] * h->n >> 20) chunks = (int)(h->lvl_px[0] * h->n >> 20);
+	if (chunks > 8) chunks = 8;
+	if (chunks < 1 || h->lvl_px[0] % 8) chunks = 1;
+	const int per = (h->n + chunks - 1) / chunks;
+	for (int c = 0, first = 0; first < h->n; c++, first += per) {
+		const int count = first + per <= h->n ? per : h->n - first;
+		const size_t off = (size_t)first * h->lvl_px[0];
+		rc = stage_h2d(d_cur + off, imgs + off, (size_t)count * h->lvl_px[0], h->h_stage + off, h->st_copy);
+		if (rc != AOF_OK) return rc;
+		AOF_CUDA(cudaEventRecord(h->ev_chunk[c], h->st_copy));
+		AOF_CUDA(cudaStreamWaitEvent(h->st, h->ev_chunk[c], 0));
+		rc = run_range(h, nxt, h->d_t, h->d_out, h->d_raw, first, count, h->st);
+		if (rc != AOF_OK) return rc;
+	}
+	h->cur = nxt;
+	h->have_prev = h->have_feat_prev = true;
 	AOF_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
 	if (raw) AOF_CUDA(cudaMemcpyAsync(h->h_raw, h->d_raw, sizeof(aof_lk_raw) * h->n, cudaMemcpyDeviceToHost, h->st));
 	AOF_CUDA(cudaStreamSynchronize(h->st));

@@ -15,7 +15,8 @@ struct aof_px4 {
 	int n = 0, device = 0;
 	SadGeom g{};
 	size_t frame_bytes = 0;
-	cudaStream_t st = nullptr;
+	cudaStream_t st = nullptr, st_copy = nullptr;
+	cudaEvent_t ev_chunk[8] = {};    // host-batch path: chunk c of the frames has landed
 	bool primed = false;
 	const uint8_t *d_prev = nullptr; // previous frames of all streams (own buffer or the caller's)
 	// state + results
@@ -81,7 +82,10 @@ int aof_px4_create(const aof_px4_params *p, int n_streams, int device, aof_px4 *
 	g.feat_thr = (uint32_t)p->flow_feature_threshold;
 	g.val_thr = (uint32_t)p->flow_value_threshold;
 	cudaError_t e;
+	for (int c = 0; c < 8; c++)
+		if (cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming) != cudaSuccess) h->ev_chunk[c] = nullptr;
 	if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess ||
+	    (e = cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_lim, sizeof(LimiterState) * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_raw, sizeof(aof_px4_raw) * n_streams)) != cudaSuccess ||
 	    (e = cudaMemset(h->d_lim, 0, sizeof(LimiterState) * n_streams)) != cudaSuccess) {
@@ -103,6 +107,9 @@ void aof_px4_destroy(aof_px4 *h)
 	cudaFreeHost(h->h_stage); cudaFreeHost(h->h_t); cudaFreeHost(h->h_out);
 	cudaFree(h->d_t); cudaFree(h->d_out);
 	cudaFree(h->d_pp); cudaFree(h->d_pc); cudaFree(h->d_praw); cudaFree(h->d_pblk);
+	for (int c = 0; c < 8; c++)
+		if (h->ev_chunk[c]) cudaEventDestroy(h->ev_chunk[c]);
+	if (h->st_copy) cudaStreamDestroy(h->st_copy);
 	if (h->st) cudaStreamDestroy(h->st);
 	delete h;
 }
@@ -155,20 +162,40 @@ static int ensure_batch_buffers(aof_px4 *h)
 	return AOF_OK;
 }
 
+// Host frames in, results out.  Up to 8 chunks of whole streams: chunk c + 1 crosses PCIe on the copy stream while the
+// kernels of chunk c run.
 int aof_px4_calc_flow_batch(aof_px4 *h, const uint8_t *imgs, const uint32_t *t_us, aof_flow_out *out)
 {
 	if (!h || !imgs || !t_us || !out) { set_error("calc_flow_batch: null argument"); return AOF_ERR_INVALID; }
 	AOF_CUDA(cudaSetDevice(h->device));
 	int rc = ensure_batch_buffers(h);
 	if (rc != AOF_OK) return rc;
-	const size_t total = h->frame_bytes * h->n;
 	uint8_t *d_cur = h->d_frames[h->slot];
-	rc = stage_h2d(d_cur, imgs, total, h->h_stage, h->st);
-	if (rc != AOF_OK) return rc;
 	memcpy(h->h_t, t_us, sizeof(uint32_t) * h->n);
 	AOF_CUDA(cudaMemcpyAsync(h->d_t, h->h_t, sizeof(uint32_t) * h->n, cudaMemcpyHostToDevice, h->st));
-	rc = aof_px4_calc_flow_device(h, d_cur, h->d_t, h->d_out, nullptr, nullptr, h->st);
-	if (rc != AOF_OK) return rc;
+	if (!h->primed) { // first frame: remember it, report quality 0 (flow_px4.cpp:73-78)
+		rc = stage_h2d(d_cur, imgs, h->frame_bytes * h->n, h->h_stage, h->st);
+		if (rc != AOF_OK) return rc;
+		rc = aof_px4_calc_flow_device(h, d_cur, h->d_t, h->d_out, nullptr, nullptr, h->st);
+		if (rc != AOF_OK) return rc;
+	} else {
+		int chunks = (int)(h->frame_bytes * h->n >> 21);   // >= 2 MiB per chunk
+		if (chunks > 8) chunks = 8;
+		if (chunks < 1) chunks = 1;
+		const int per = (h->n + chunks - 1) / chunks;
+		for (int c = 0, first = 0; first < h->n; c++, first += per) {
+			const int count = first + per <= h->n ? per : h->n - first;
+			const size_t off = (size_t)first * h->frame_bytes;
+			rc = stage_h2d(d_cur + off, imgs + off, (size_t)count * h->frame_bytes, h->h_stage + off, h->st_copy);
+			if (rc != AOF_OK) return rc;
+			AOF_CUDA(cudaEventRecord(h->ev_chunk[c], h->st_copy));
+			AOF_CUDA(cudaStreamWaitEvent(h->st, h->ev_chunk[c], 0));
+			AOF_CUDA(sad_flow_launch(h->p.search_size, h->d_prev + off, d_cur + off, h->g, count, h->d_raw + first, nullptr, h->st));
+			AOF_CUDA(px4_epilogue_launch(h->d_raw + first, h->d_t + first, h->d_lim + first, h->d_out + first, count,
+						     h->p.output_rate, h->p.focal_length_x, h->p.focal_length_y, h->st));
+		}
+		h->d_prev = d_cur;
+	}
 	AOF_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
 	AOF_CUDA(cudaStreamSynchronize(h->st));
 	memcpy(out, h->h_out, sizeof(aof_flow_out) * h->n);
