@@ -80,6 +80,10 @@ private:
 
 cudaError_t sad_flow_launch(int search, const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n,
 			    aof_px4_raw *raw, aof_px4_block *blocks, cudaStream_t st);
+// second version (sad_flow2.cu): pre-shifted copies of the current frame, 8-lane half-pixel stage
+bool sad_flow2_supported(const SadGeom &g);
+cudaError_t sad_flow2_launch(int search, const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n,
+			     aof_px4_raw *raw, aof_px4_block *blocks, cudaStream_t st);
 cudaError_t px4_epilogue_launch(const aof_px4_raw *raw, const uint32_t *t_us, LimiterState *lim, aof_flow_out *out,
 				int n, int output_rate, float fx, float fy, cudaStream_t st);
 

@@ -287,6 +287,11 @@ cudaError_t sad_flow_launch(int search, const uint8_t *prev, const uint8_t *cur,
 			    aof_px4_raw *raw, aof_px4_block *blocks, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
+	if (sad_flow2_supported(g)) {
+		KernelTimer kt(KID_SAD_FLOW, st);
+		count_launch();
+		return sad_flow2_launch(search, prev, cur, g, n, raw, blocks, st);
+	}
 	switch (search) {
 	case 4: return launch_sad<4>(prev, cur, g, n, raw, blocks, st);
 	case 6: return launch_sad<6>(prev, cur, g, n, raw, blocks, st);

@@ -30,13 +30,14 @@ import __graft_entry__ as entry  # noqa: E402
 
 FX, FY = 216.6677, 216.2457
 # ---- SAD workload
-SAD_STREAMS, SAD_W, SAD_H, SAD_SEARCH, SAD_ROT = 4096, 64, 64, 4, 16
+SAD_STREAMS, SAD_W, SAD_H, SAD_SEARCH, SAD_ROT = int(os.environ.get("AOF_BENCH_SAD_STREAMS", "4096")), 64, 64, 4, 16
 SAD_BYTES_PER_PAIR = 2 * SAD_W * SAD_H + 16      # both frames read + 16 B result
 SAD_INSTR_PER_PAIR = 40550                       # packed-byte instructions of the reference algorithm
 # ---- LK workload (SURVEY.md 8(d), config 2 batched)
 LK_STREAMS, LK_W, LK_H, LK_FEATURES, LK_ROT = 512, 640, 480, 20, 4
 LK_LEVEL_PX = [640 * 480, 320 * 240, 160 * 120, 80 * 60]
 LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read once + L1..L3 written = 408 000 B
+LK_FAST_OPS_PER_PIXEL_PAIR = 88                             # 16 ring differences + 72 packed min/max
 
 
 def peaks():
@@ -460,10 +461,28 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     pk = peaks()
     dom = max(kb, key=lambda kname: kb[kname]["ms_per_step"])
     step_ms = ms / args.steps
-    # algorithmic bytes per launch of the dominant kernel
-    alg = {"lk_pyr_down_kernel": n * (LK_LEVEL_PX[0] + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0,
-           "lk_pyr_fused_kernel": n * LK_BYTES_PER_PAIR, "lk_fast_kernel": n * LK_LEVEL_PX[0]}
-    dom_bytes = alg.get(dom, n * LK_BYTES_PER_PAIR)
+    # per-kernel rooflines: algorithmic bytes / packed integer operations per launch
+    px0 = LK_LEVEL_PX[0]
+    alg_bytes = {"lk_pyr_down_kernel": n * (px0 + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0,
+                 "lk_pyr_fused_kernel": n * LK_BYTES_PER_PAIR,      # level 0 read once + levels 1..3 written
+                 "lk_fast_kernel": n * px0}                          # level 0 of the bins that need features
+    # FAST response: 16 differences + 72 packed min/max (the arc-pair network) per PAIR of pixels, every pixel scored
+    alg_alu = {"lk_fast_kernel": n * (px0 / 2.0) * LK_FAST_OPS_PER_PIXEL_PAIR}
+    kroof = {}
+    for kname, kv in kb.items():
+        k_ms = kv["ms_per_step"] / max(1.0, kv["launches_per_step"])
+        e = {"kernel_ms": k_ms}
+        if kname in alg_bytes:
+            a = alg_bytes[kname] / (k_ms * 1e-3) / 1e9
+            e["hbm"] = {"achieved": a, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": a / pk["hbm_gbs"],
+                        "algorithmic_bytes_per_launch": alg_bytes[kname]}
+        if kname in alg_alu and "alu_packed_instr_per_s" in pk:
+            a = alg_alu[kname] / (k_ms * 1e-3)
+            e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed u16x2 instr/s",
+                            "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_launch": alg_alu[kname]}
+        e["bound"] = {"lk_pyr_fused_kernel": "hbm", "lk_pyr_down_kernel": "hbm", "lk_fast_kernel": "int-alu"}.get(kname, "latency")
+        kroof[kname] = e
+    dom_bytes = alg_bytes.get(dom, n * LK_BYTES_PER_PAIR)
     dom_ms = kb[dom]["ms_per_step"] / max(1.0, kb[dom]["launches_per_step"])
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
     r = {
@@ -476,10 +495,12 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk["which"],
                      "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
+                     "note": "dominant kernel by time; its binding roofline is in kernel_rooflines[kernel][bound] "
+                             "(lk_fast_kernel is integer-ALU bound, the HBM-bound kernel of the step is lk_pyr_fused_kernel)",
                      "step": {"algorithmic_bytes_per_step": n * LK_BYTES_PER_PAIR,
                               "achieved": n * LK_BYTES_PER_PAIR / (step_ms * 1e-3) / 1e9,
                               "frac": n * LK_BYTES_PER_PAIR / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"]}},
-        "kernels": kb,
+        "kernels": kb, "kernel_rooflines": kroof,
         "e2e": {"value": world * n * e_steps / (e2e_ms * 1e-3), "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
                 "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)"},
@@ -528,7 +549,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": p["dtype"], "data": "synthetic", "config": p["config"], "roofline": p["roofline"],
             "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
-    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu"):
+    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu", "kernel_rooflines"):
         if key in p:
             line[key] = p[key]
     if args.workload == "both":
