@@ -331,14 +331,19 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 
 // ---------------------------------------------------------------------------
 // K6 driver + trackFeatures bookkeeping + per-bin demand.  One CTA per stream.
-constexpr int TU_WARPS = 16;
+#ifndef AOF_TU_WARPS
+#define AOF_TU_WARPS 8
+#endif
+constexpr int TU_WARPS = AOF_TU_WARPS;
 
 __global__ void __launch_bounds__(TU_WARPS * 32)
 lk_track_update_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev)
 {
 	__shared__ LkWarpScratch s_sc[TU_WARPS];
-	__shared__ float2 s_next[LK_MAX_FEATURES];
+	__shared__ float2 s_next[LK_MAX_FEATURES], s_pc[LK_MAX_FEATURES];
+	__shared__ int s_uv[LK_MAX_FEATURES];
 	__shared__ uint8_t s_lk_status[LK_MAX_FEATURES];
+	__shared__ int s_per_bin[LK_BINS];
 	const size_t stream = blockIdx.x;
 	const int N = g.n_feat;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -348,56 +353,54 @@ lk_track_update_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_pre
 	float2 *fc = s.feat_cur + stream * N;
 	const int npc = s.n_prev_corners[stream];
 	const bool do_lk = have_prev && npc > 0;
+	// the per-stream state is staged in shared memory once: everything below that walks over the slots would
+	// otherwise be a chain of dependent global loads
+	for (int i = threadIdx.x; i < N; i += blockDim.x) { s_uv[i] = uv[i]; s_pc[i] = pc[i]; }
+	if (threadIdx.x < LK_BINS) { s_per_bin[threadIdx.x] = 0; s.kp_count[stream * LK_BINS + threadIdx.x] = 0; }
+	__syncthreads();
 	if (do_lk) {
 		// only slots that were active can influence anything downstream; the reference tracks
 		// the stale ones too (trackFeatures.cpp:98) but never reads them again before they are reassigned
 		for (int f = warp; f < npc; f += TU_WARPS) {
-			if (uv[f] != 1) continue;
-			const float2 p = pc[f];
+			if (s_uv[f] != 1) continue;
+			const float2 p = s_pc[f];
 			float ox, oy;
 			const int st = lk_track_point(g, prev, next, stream, p.x, p.y, s_sc[warp], ox, oy);
 			if (lane == 0) { s_next[f] = make_float2(ox, oy); s_lk_status[f] = (uint8_t)st; }
 		}
 	}
 	__syncthreads();
-	// trackFeatures.cpp:77-125, one thread per slot
+	// trackFeatures.cpp:77-125, one thread per slot; then the demand of initMorePoints (:144-183): bin = x * 4 + y
+	int wants = 0;
 	for (int i = threadIdx.x; i < N; i += blockDim.x) {
-		int status = uv[i];
+		int status = s_uv[i];
 		int pst = status == 1;
 		float2 feat = make_float2(-100.f, -100.f);
+		float2 corner = s_pc[i];
 		if (do_lk && i < npc) {
 			if (pst) {
-				pc[i] = s_next[i];
+				corner = s_next[i];
+				pc[i] = corner;
 				if (!s_lk_status[i]) pst = 0;
 			}
 			if (pst) {
-				const float2 c = s_next[i];
-				if (c.x < 0.f || c.x > (float)g.w[0] || c.y < 0.f || c.y > (float)g.h[0]) status = 0;
-				else { feat = c; status = 1; }
+				if (corner.x < 0.f || corner.x > (float)g.w[0] || corner.y < 0.f || corner.y > (float)g.h[0]) status = 0;
+				else { feat = corner; status = 1; }
 			} else if (status == 1) status = 0;
 		}
 		ps[i] = (uint8_t)pst;
 		uv[i] = status;
 		fc[i] = feat;
+		wants += status == 2;
+		if (i < npc && status == 1) {
+			const int bx = (int)__fdiv_rn(corner.x, (float)g.bw), by = (int)__fdiv_rn(corner.y, (float)g.bh);
+			if (bx < 4 && by < 4) atomicAdd(&s_per_bin[bx * 4 + by], 1);
+		}
 	}
-	__syncthreads();
-	// initMorePoints demand (trackFeatures.cpp:144-183): bin = x * 4 + y
-	if (threadIdx.x < LK_BINS) s.kp_count[stream * LK_BINS + threadIdx.x] = 0;
-	if (threadIdx.x == 0) {
-		int target = 0;
-		int per_bin[LK_BINS];
-		for (int b = 0; b < LK_BINS; b++) per_bin[b] = 0;
-		for (int i = 0; i < N; i++) target += uv[i] == 2;
-		for (int i = 0; i < npc; i++)
-			if (uv[i] == 1) {
-				const int bx = (int)__fdiv_rn(pc[i].x, (float)g.bw), by = (int)__fdiv_rn(pc[i].y, (float)g.bh);
-				if (bx >= 4 || by >= 4) continue;
-				per_bin[bx * 4 + by]++;
-			}
-		for (int b = 0; b < LK_BINS; b++)
-			s.bin_needed[stream * LK_BINS + b] = target ? max(0, g.tpb - per_bin[b]) : 0;
-		s.target[stream] = target;
-	}
+	const int target = __syncthreads_count(wants); // N <= blockDim.x: at most one slot per thread
+	if (threadIdx.x < LK_BINS)
+		s.bin_needed[stream * LK_BINS + threadIdx.x] = target ? max(0, g.tpb - s_per_bin[threadIdx.x]) : 0;
+	if (threadIdx.x == 0) s.target[stream] = target;
 }
 
 cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
@@ -590,7 +593,10 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 // "The first acceptable one in sorted order" is an arg-max under the gate, and a
 // point rejected once stays rejected because the set it is tested against only
 // grows -- so each pick is one masked warp/block arg-max, no sort.
-constexpr int SEL_THREADS = 512;
+#ifndef AOF_SEL_THREADS
+#define AOF_SEL_THREADS 256
+#endif
+constexpr int SEL_THREADS = AOF_SEL_THREADS;
 constexpr int SEL_MAX_TPB = (LK_MAX_FEATURES - 1) / LK_BINS + 1; // 7
 constexpr int SEL_MAX_GOOD = LK_BINS * SEL_MAX_TPB + LK_MAX_FEATURES;
 
@@ -641,13 +647,21 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 	float2 *fp = s.feat_prev + stream * N;
 	const int target = s.target[stream];
 	int fast_bins = 0;
+	// the per-stream state is staged in shared memory: the order-dependent parts below run on one thread and
+	// would otherwise be chains of dependent global loads
+	__shared__ float2 s_pc[LK_MAX_FEATURES], s_fc[LK_MAX_FEATURES], s_fp[LK_MAX_FEATURES];
+	__shared__ int s_uv[LK_MAX_FEATURES];
+	__shared__ uint8_t s_ps[LK_MAX_FEATURES];
+	__shared__ int s_fast_bins;
+	for (int i = tid; i < N; i += SEL_THREADS) { s_pc[i] = pc[i]; s_fc[i] = fc[i]; s_fp[i] = fp[i]; s_uv[i] = uv[i]; s_ps[i] = ps[i]; }
+	__syncthreads();
 
 	if (target > 0) { // uniform over the CTA
 		const int npc = s.n_prev_corners[stream];
 		if (tid == 0) {
 			int n = 0;
 			for (int j = 0; j < npc; j++)
-				if (ps[j]) { s_ex[n] = (int)pc[j].x; s_ey[n] = (int)pc[j].y; n++; }
+				if (s_ps[j]) { s_ex[n] = (int)s_pc[j].x; s_ey[n] = (int)s_pc[j].y; n++; }
 			s_nex = n;
 		}
 		if (tid < LK_BINS) {
@@ -658,8 +672,9 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 		__syncthreads();
 		const int nex = s_nex;
 		// ---- stage 1: one warp per bin
-		if (warp < LK_BINS && s_needed[warp] > 0) {
-			const int b = warp, needed = s_needed[b], cnt = s_cnt[b];
+		for (int b = warp; b < LK_BINS; b += SEL_THREADS / 32) {
+			if (s_needed[b] <= 0) continue;
+			const int needed = s_needed[b], cnt = s_cnt[b];
 			const int c0 = (b >> 2) * g.bw, r0 = (b & 3) * g.bh;
 			const uint32_t *list = s.kp + (stream * LK_BINS + b) * (size_t)g.kp_cap;
 			int npick = 0;
@@ -745,86 +760,92 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 		}
 		if (tid < LK_BINS) fast_bins = s_needed[tid] > 0;
 	}
-	if (tid >= 32) return;
-	fast_bins = __reduce_add_sync(0xFFFFFFFFu, fast_bins);
-	if (tid != 0) return;
-
-	// ---- stage 4: slot assignment (trackFeatures.cpp:306-362)
-	if (target > 0) {
-		const int ngood = s_ngood;
-		if (!ngood) {
-			for (int i = 0; i < N; i++)
-				if (uv[i] == 2) uv[i] = 0;
-		} else {
-			if (s.n_prev_corners[stream] < N) {
-				for (int i = s.n_prev_corners[stream]; i < N; i++) pc[i] = make_float2(0.f, 0.f);
-				s.n_prev_corners[stream] = N;
-			}
-			int m = 0;
-			for (int i = 0; i < N; i++) {
-				if (uv[i] != 2) continue;
-				if (m < ngood) {
-					const float2 p = make_float2((float)s_gx[m], (float)s_gy[m]);
-					pc[i] = p; fc[i] = p; ps[i] = 1;
-					m++;
-				} else uv[i] = 0;
+	if (tid < 32) {
+		fast_bins = __reduce_add_sync(0xFFFFFFFFu, fast_bins);
+		if (tid == 0) s_fast_bins = fast_bins;
+	}
+	if (tid == 0) {
+		// ---- stage 4: slot assignment (trackFeatures.cpp:306-362)
+		if (target > 0) {
+			const int ngood = s_ngood;
+			if (!ngood) {
+				for (int i = 0; i < N; i++)
+					if (s_uv[i] == 2) s_uv[i] = 0;
+			} else {
+				if (s.n_prev_corners[stream] < N) {
+					for (int i = s.n_prev_corners[stream]; i < N; i++) s_pc[i] = make_float2(0.f, 0.f);
+					s.n_prev_corners[stream] = N;
+				}
+				int m = 0;
+				for (int i = 0; i < N; i++) {
+					if (s_uv[i] != 2) continue;
+					if (m < ngood) {
+						const float2 p = make_float2((float)s_gx[m], (float)s_gy[m]);
+						s_pc[i] = p; s_fc[i] = p; s_ps[i] = 1;
+						m++;
+					} else s_uv[i] = 0;
+				}
 			}
 		}
-	}
 
-	// ---- optional undistortion of every slot, placeholders included (flow_opencv.cpp:108-119)
-	if (cam.on)
-		for (int i = 0; i < N; i++) fc[i] = lk_undistort(cam, fc[i]);
+		// ---- optional undistortion of every slot, placeholders included (flow_opencv.cpp:108-119)
+		if (cam.on)
+			for (int i = 0; i < N; i++) s_fc[i] = lk_undistort(cam, s_fc[i]);
 
-	// ---- calcFlow statistics (flow_opencv.cpp:121-180)
-	int meancount = 0, active = 0;
-	float mx = 0.f, my = 0.f;
-	if (have_feat_prev) {
-		for (int i = 0; i < N; i++)
-			if (uv[i] == 1) { mx += fc[i].x - fp[i].x; my += fc[i].y - fp[i].y; meancount++; }
-		active = meancount;
-		if (meancount) {
-			mx /= (float)meancount; my /= (float)meancount;
-			float sx = 0.f, sy = 0.f;
+		// ---- calcFlow statistics (flow_opencv.cpp:121-180)
+		int meancount = 0, active = 0;
+		float mx = 0.f, my = 0.f;
+		if (have_feat_prev) {
 			for (int i = 0; i < N; i++)
-				if (uv[i] == 1) {
-					const float ex = fc[i].x - fp[i].x - mx, ey = fc[i].y - fp[i].y - my;
-					sx = (float)((double)sx + (double)ex * (double)ex); // pow(float, 2) runs in double
-					sy = (float)((double)sy + (double)ey * (double)ey);
-				}
-			sx = sqrtf(sx / (float)meancount); sy = sqrtf(sy / (float)meancount);
-			float tx = 0.f, ty = 0.f;
-			meancount = 0;
-			for (int i = 0; i < N; i++)
-				if (uv[i] == 1) {
-					const float fx = fc[i].x - fp[i].x, fy = fc[i].y - fp[i].y;
-					if (fabsf(fx - mx) < sx * conf && fabsf(fy - my) < sy * conf) { tx += fx; ty += fy; meancount++; }
-					else uv[i] = 0;
-				}
-			if (meancount) { mx = tx / (float)meancount; my = ty / (float)meancount; }
+				if (s_uv[i] == 1) { mx += s_fc[i].x - s_fp[i].x; my += s_fc[i].y - s_fp[i].y; meancount++; }
+			active = meancount;
+			if (meancount) {
+				mx /= (float)meancount; my /= (float)meancount;
+				float sx = 0.f, sy = 0.f;
+				for (int i = 0; i < N; i++)
+					if (s_uv[i] == 1) {
+						const float ex = s_fc[i].x - s_fp[i].x - mx, ey = s_fc[i].y - s_fp[i].y - my;
+						sx = (float)((double)sx + (double)ex * (double)ex); // pow(float, 2) runs in double
+						sy = (float)((double)sy + (double)ey * (double)ey);
+					}
+				sx = sqrtf(sx / (float)meancount); sy = sqrtf(sy / (float)meancount);
+				float tx = 0.f, ty = 0.f;
+				meancount = 0;
+				for (int i = 0; i < N; i++)
+					if (s_uv[i] == 1) {
+						const float fx = s_fc[i].x - s_fp[i].x, fy = s_fc[i].y - s_fp[i].y;
+						if (fabsf(fx - mx) < sx * conf && fabsf(fy - my) < sy * conf) { tx += fx; ty += fy; meancount++; }
+						else s_uv[i] = 0;
+					}
+				if (meancount) { mx = tx / (float)meancount; my = ty / (float)meancount; }
+			}
+		}
+		const int q0 = (int)round(255.0 * (double)meancount / (double)N);
+		LimiterState l = s.lim[stream];
+		aof_flow_out o;
+		float fx = mx, fy = my;
+		o.quality = limit_rate(l, output_rate, q0, t_us[stream], o.dt_us, fx, fy);
+		o.flow_x = (float)atan2((double)fx, (double)focal_x);
+		o.flow_y = (float)atan2((double)fy, (double)focal_y);
+		s.lim[stream] = l;
+		out[stream] = o;
+		if (raw) {
+			aof_lk_raw r;
+			r.px_x = mx; r.px_y = my; r.inliers = meancount; r.active = active; r.fast_bins = s_fast_bins; r.quality = q0;
+			raw[stream] = r;
 		}
 	}
-	// features_previous = features_current; status machine (flow_opencv.cpp:183-196)
-	for (int i = 0; i < N; i++) {
-		fp[i] = fc[i];
-		int u = uv[i];
+	__syncthreads();
+	// features_previous = features_current; status machine (flow_opencv.cpp:183-196); write the state back
+	for (int i = tid; i < N; i += SEL_THREADS) {
+		int u = s_uv[i];
 		if (u == 2) u = 1;
-		if (u == 0) u = 2;
+		else if (u == 0) u = 2;
 		uv[i] = u;
-	}
-	const int q0 = (int)round(255.0 * (double)meancount / (double)N);
-	LimiterState l = s.lim[stream];
-	aof_flow_out o;
-	float fx = mx, fy = my;
-	o.quality = limit_rate(l, output_rate, q0, t_us[stream], o.dt_us, fx, fy);
-	o.flow_x = (float)atan2((double)fx, (double)focal_x);
-	o.flow_y = (float)atan2((double)fy, (double)focal_y);
-	s.lim[stream] = l;
-	out[stream] = o;
-	if (raw) {
-		aof_lk_raw r;
-		r.px_x = mx; r.px_y = my; r.inliers = meancount; r.active = active; r.fast_bins = fast_bins; r.quality = q0;
-		raw[stream] = r;
+		fp[i] = s_fc[i];
+		fc[i] = s_fc[i];
+		pc[i] = s_pc[i];
+		ps[i] = s_ps[i];
 	}
 }
 

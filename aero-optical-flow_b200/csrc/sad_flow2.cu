@@ -24,16 +24,20 @@
 
 namespace aof {
 
-// per-byte (a + b) >> 1 in three ALU instructions: LOP3, LOP3, LEA.HI
-__device__ __forceinline__ uint32_t havg4_3(uint32_t a, uint32_t b)
+// per-byte (a + b) >> 1 = (a & b) + (((a ^ b) & 0xFE..FE) >> 1): two LOP3 on the ALU pipe and one IMAD.HI on the
+// otherwise idle FMA pipe (x >> 1 == hi32(x * 2^31)).  `half` must hold 0x80000000 in a register the compiler cannot
+// see through, or ptxas turns the multiply back into a shift on the ALU pipe.
+__device__ __forceinline__ uint32_t havg4_3(uint32_t a, uint32_t b, uint32_t half)
 {
-	return (a & b) + __umulhi((a ^ b) & 0xFEFEFEFEu, 0x80000000u);
+	uint32_t r;
+	asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"((a ^ b) & 0xFEFEFEFEu), "r"(half), "r"(a & b));
+	return r;
 }
 
 template <int S>
 __global__ void __launch_bounds__(32)
 sad_flow2_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ cur, SadGeom g, int n,
-		 aof_px4_raw *__restrict__ raw, aof_px4_block *__restrict__ blocks)
+		 aof_px4_raw *__restrict__ raw, aof_px4_block *__restrict__ blocks, uint32_t half_mul /* 0x80000000, see havg4_3 */)
 {
 	constexpr int NI = 2 * S + 1;
 	constexpr int ROWS = 8 + 2 * S;
@@ -201,10 +205,10 @@ sad_flow2_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 					const uint32_t Y = bytes_at(u1, u2, sh);       // q[3..6]
 					const uint32_t Q = __byte_perm(X, Y, 0x4321);  // q[0..3]
 					const uint32_t Qp = __byte_perm(X, Y, 0x5432); // q[1..4]
-					const uint32_t H4 = havg4_3(Q, X);
-					const uint32_t H0 = havg4_3(Q, Qp);
+					const uint32_t H4 = havg4_3(Q, X, half_mul);
+					const uint32_t H0 = havg4_3(Q, Qp, half_mul);
 					if (rr >= 1) {
-						const uint32_t V = havg4_3(pQ, Q), T0 = havg4_3(pH0, H0), T4 = havg4_3(pH4, H4);
+						const uint32_t V = havg4_3(pQ, Q, half_mul), T0 = havg4_3(pH0, H0, half_mul), T4 = havg4_3(pH4, H4, half_mul);
 						if (rr >= 2) { // block row i = rr - 2 is the previous window row; pV.. belong to rows (i - 1, i)
 							const uint32_t ai = s_ablk[b][2 * (rr - 2) + half];
 							acc[0] = sad4(ai, pH0, acc[0]);
@@ -314,7 +318,7 @@ template <int S> static cudaError_t launch_sad2(const uint8_t *prev, const uint8
 	if (env && atoi(env) > 0 && atoi(env) < occ) occ = atoi(env);
 	long long grid = (long long)sms[dev] * occ;
 	if (grid > n) grid = n;
-	sad_flow2_kernel<S><<<(unsigned)grid, 32, dyn, st>>>(prev, cur, g, n, raw, blocks);
+	sad_flow2_kernel<S><<<(unsigned)grid, 32, dyn, st>>>(prev, cur, g, n, raw, blocks, 0x80000000u);
 	return cudaGetLastError();
 }
 
