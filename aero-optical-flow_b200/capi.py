@@ -48,6 +48,8 @@ class DenseParams(C.Structure):
                 ("flow_feature_threshold", C.c_int), ("flow_value_threshold", C.c_int)]
 
 
+ae_stats_dtype = np.dtype([("hist", np.uint32, (10,)), ("msv", np.float32), ("pad", np.uint32)])
+
 dense_block_dtype = np.dtype([("dx", np.int16), ("dy", np.int16), ("subdir", np.int16), ("flags", np.int16),
                               ("best_sad", np.uint32), ("texture", np.uint32)])
 
@@ -108,6 +110,12 @@ def lib():
     L.aof_gftt_destroy.restype = None
     L.aof_gftt_min_eig.argtypes = [vp, u8p, C.c_int, vp]
     L.aof_gftt_detect.argtypes = [vp, u8p, C.c_int, C.c_int, C.c_double, C.c_double, vp, vp]
+    L.aof_host_register.argtypes = [vp, C.c_size_t]
+    L.aof_host_unregister.argtypes = [vp]
+    L.aof_crop_to_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+    L.aof_ae_stats_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
+    L.aof_ae_stats_host.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    L.aof_pack_optical_flow_rad.argtypes = [vp, C.c_int, C.c_uint64, vp, vp, C.c_uint8, C.c_uint8, vp, vp, C.c_int, vp]
     _lib = L
     return L
 
@@ -342,3 +350,38 @@ class Gftt:
         check(lib().aof_gftt_detect(self.handle, _ptr(imgs), n, max_corners, quality, min_distance, _ptr(xy), _ptr(cnt)),
               "aof_gftt_detect")
         return [xy[i, :cnt[i]] for i in range(n)]
+
+
+# ---- the steps either side of calcFlow (include/aof.h "callers / consumers") ----------------
+
+def ae_stats(frames, device=0):
+    """auto-exposure statistics (src/mainloop.cpp:197-220) of n host frames [n, h, w] -> ae_stats_dtype[n]"""
+    frames = np.ascontiguousarray(frames, np.uint8)
+    n, h, w = frames.shape
+    out = np.zeros(n, ae_stats_dtype)
+    check(lib().aof_ae_stats_host(_ptr(frames), n, w, h, device, _ptr(out)), "aof_ae_stats_host")
+    return out
+
+
+def pack_optical_flow_rad(res, time_offset_us, img_time_us, gyro_xyz, system_id, component_id, seq):
+    """MAVLink 2 OPTICAL_FLOW_RAD frames of the published results (quality >= 0).
+    -> (bytes, frame offsets[n] (-1 = not published), next seq)"""
+    res = np.ascontiguousarray(res, flow_out_dtype)
+    n = len(res)
+    t = np.ascontiguousarray(img_time_us, np.uint32)
+    g = np.ascontiguousarray(gyro_xyz, np.float64).reshape(n, 3)
+    buf = np.zeros(56 * max(n, 1), np.uint8)
+    off = np.zeros(max(n, 1), np.int32)
+    sq = np.array([seq], np.uint8)
+    used = check(lib().aof_pack_optical_flow_rad(_ptr(res), n, time_offset_us, _ptr(t), _ptr(g), system_id, component_id,
+                                                 _ptr(sq), _ptr(buf), len(buf), _ptr(off)), "aof_pack_optical_flow_rad")
+    return buf[:used].tobytes(), off[:n], int(sq[0])
+
+
+def crop_to_device(cam_frames, w, h, d_batch_ptr, stream=0):
+    """centre crops of host camera frames [n, cam_h, cam_w] -> contiguous device batch (strided H2D DMA, no host copy)"""
+    cam_frames = np.ascontiguousarray(cam_frames, np.uint8)
+    n, ch, cw = cam_frames.shape
+    ptrs = (C.c_void_p * n)(*[cam_frames[i].ctypes.data for i in range(n)])
+    check(lib().aof_crop_to_device(ptrs, n, cw, ch, w, h, C.c_void_p(d_batch_ptr), C.c_void_p(stream)), "aof_crop_to_device")
+    return cam_frames  # keep alive until the stream has been synchronised

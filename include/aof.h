@@ -22,6 +22,7 @@
 #ifndef AOF_B200_H
 #define AOF_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -241,6 +242,46 @@ int aof_gftt_min_eig(aof_gftt *g, const uint8_t *imgs, int n, float *eig);
 /* xy[n * max_corners * 2] (x, y), counts[n]; corners in cv's order (response desc, address desc) */
 int aof_gftt_detect(aof_gftt *g, const uint8_t *imgs, int n, int max_corners, double quality_level, double min_distance,
 		    float *xy, int *counts);
+
+/* ------------------------------------------- callers / consumers either side of the path */
+
+/* (f1) centre crop + staging.  The reference wraps the camera buffer in a Mat, takes the centre ROI of
+ * image_width x image_height and copies it to a contiguous Mat before calcFlow (src/mainloop.cpp:294-298,317-320).
+ * Here the crop is the DMA itself: one strided host->device copy per camera frame, straight from the camera buffer
+ * (register page-aligned V4L2 USERPTR buffers once with aof_host_register, src/camera.cpp:97-115) into the contiguous
+ * device batch the calc_flow_device entry points take.  frames[i] = top-left of camera frame i (cam_w x cam_h, stride
+ * cam_w); d_batch receives n crops of w x h.  Asynchronous on cuda_stream. */
+int aof_host_register(void *ptr, size_t bytes);
+int aof_host_unregister(void *ptr);
+int aof_crop_to_device(const uint8_t *const *frames, int n, int cam_w, int cam_h, int w, int h, uint8_t *d_batch,
+		       void *cuda_stream);
+
+/* (f3) auto-exposure statistics of Mainloop::_exposure_update (src/mainloop.cpp:197-220): 10-bin histogram
+ * (cv::calcHist, range [0, 255), i.e. value 255 is not counted) of the central 128 x 128 pixels of each frame and the
+ * mean sample value msv = sum_i (i + 1) * hist[i] / 16384 accumulated in float in that order. */
+typedef struct aof_ae_stats {
+	uint32_t hist[10];
+	float msv;
+	uint32_t pad;
+} aof_ae_stats;
+/* n frames of w x h (w, h >= 128) in DEVICE memory -> d_out[n], asynchronous on cuda_stream */
+int aof_ae_stats_device(const uint8_t *d_frames, int n, int w, int h, aof_ae_stats *d_out, void *cuda_stream);
+/* HOST frames, synchronous */
+int aof_ae_stats_host(const uint8_t *frames, int n, int w, int h, int device, aof_ae_stats *out);
+
+/* (f4) result wire format: the OPTICAL_FLOW_RAD message (id 106, 44-byte payload, CRC_EXTRA 138;
+ * modules/mavlink_c/common/mavlink_msg_optical_flow_rad.h:4-22) the reference fills at src/mainloop.cpp:359-371 and
+ * frames with mavlink_msg_optical_flow_rad_encode + mavlink_msg_to_send_buffer (src/mavlink_tcp.cpp:142-149), i.e. a
+ * MAVLink 2 frame: STX 0xFD, payload length after trimming trailing zero bytes, incompat 0, compat 0, seq, sysid,
+ * compid, 24-bit msgid, payload, X.25 CRC over everything after STX plus CRC_EXTRA.
+ * For each stream i with res[i].quality >= 0 (the reference returns early on -1, src/mainloop.cpp:328) one frame is
+ * appended to buf: time_usec = time_offset_us + img_time_us[i], integration_time_us = dt_us, integrated_x / y = flow,
+ * integrated_xgyro = -gyro[3i+1], integrated_ygyro = gyro[3i], integrated_zgyro = gyro[3i+2], distance = -1,
+ * everything else 0, quality as is; seq = (*seq)++ per frame.  frame_off[i] = offset of stream i's frame in buf or -1.
+ * Returns the number of bytes written (<= 56 per frame), or AOF_ERR_INVALID if buf_cap is too small.  Host-side. */
+int aof_pack_optical_flow_rad(const aof_flow_out *res, int n, uint64_t time_offset_us, const uint32_t *img_time_us,
+			      const double *gyro_xyz, uint8_t system_id, uint8_t component_id, uint8_t *seq,
+			      uint8_t *buf, int buf_cap, int *frame_off);
 
 /* optional per-kernel timing (CUDA events around every launch of this library; off by default).
  * aof_timing_read(k, ...) for k in [0, aof_timing_kernels()) waits for the recorded launches and
