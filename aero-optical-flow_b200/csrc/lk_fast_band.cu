@@ -75,11 +75,14 @@ __device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint3
 }
 
 // dynamic shared memory: A[FB_PROWS][P], B[FB_PROWS][P], responses[FB_SROWS][P], survivor list
-template <int THREADS>
+// PC = row pitch of the shared-memory arrays in words when it is known at compile time (84 for the 160-px bins of a
+// 640-px frame: every ring tap is then an immediate offset of one base address), 0 = run time (P_rt)
+template <int THREADS, int PC>
 __global__ void __launch_bounds__(THREADS)
-lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P,
+lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
 		    int list_cap)
 {
+	const int P = PC ? PC : P_rt;
 	extern __shared__ __align__(16) uint32_t fb_smem[];
 	uint32_t *sA = fb_smem;
 	uint32_t *sB = sA + FB_PROWS * P;
@@ -100,18 +103,33 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
 
 	// ---- pixel rows y0 - 4 .. y1 + 3 of the bin -> pair layouts (tile row t <-> bin row y0 - 4 + t)
+	// THREADS >= 8 nq, so 6 rounds cover the FB_PROWS x nq words; all loads of a thread are issued before the first use
 	const int n_prow = y1 - y0 + 8;
-	for (int i = tid; i < n_prow * nq; i += THREADS) {
-		const int t = i / nq, q = i - t * nq;
-		const int y = y0 - 4 + t;
-		if (y < 0 || y >= bh) continue;                           // rows -1 and bh only feed responses that are not computed
-		const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (size_t)y * W);
-		const uint32_t w0 = __ldg(row + q);
-		const uint32_t w1 = q + 1 < nq ? __ldg(row + q + 1) : 0u; // p[bw] is never used
-		const uint32_t a0 = __byte_perm(w0, 0u, 0x4140), a1 = __byte_perm(w0, 0u, 0x4342);
-		const uint32_t b0 = __byte_perm(w0, 0u, 0x4241), b1 = __byte_perm(__funnelshift_r(w0, w1, 24), 0u, 0x4140);
-		*reinterpret_cast<uint2 *>(sA + t * P + 2 * q) = make_uint2(a0, a1);
-		*reinterpret_cast<uint2 *>(sB + t * P + 2 * q) = make_uint2(b0, b1);
+	{
+		constexpr int LD_ROUNDS = 6;
+		const int dt = THREADS / nq, dq = THREADS - dt * nq;      // (row, word) step of one round
+		int t = tid / nq, q = tid - t * nq;
+		uint32_t w0[LD_ROUNDS], w1[LD_ROUNDS];
+		int tt[LD_ROUNDS], qq[LD_ROUNDS];
+#pragma unroll
+		for (int k = 0; k < LD_ROUNDS; k++) {
+			const int y = y0 - 4 + t;
+			const bool on = t < n_prow && y >= 0 && y < bh;       // rows -1 and bh only feed responses that are not computed
+			tt[k] = on ? t : -1; qq[k] = q;
+			const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (size_t)(on ? y : 0) * W);
+			w0[k] = __ldg(row + q);
+			w1[k] = __ldg(row + (q + 1 < nq ? q + 1 : q));        // p[bw] is never used
+			t += dt; q += dq;
+			if (q >= nq) { q -= nq; t++; }
+		}
+#pragma unroll
+		for (int k = 0; k < LD_ROUNDS; k++) {
+			if (tt[k] < 0) continue;
+			const uint32_t a0 = __byte_perm(w0[k], 0u, 0x4140), a1 = __byte_perm(w0[k], 0u, 0x4342);
+			const uint32_t b0 = __byte_perm(w0[k], 0u, 0x4241), b1 = __byte_perm(__funnelshift_r(w0[k], w1[k], 24), 0u, 0x4140);
+			*reinterpret_cast<uint2 *>(sA + tt[k] * P + 2 * qq[k]) = make_uint2(a0, a1);
+			*reinterpret_cast<uint2 *>(sB + tt[k] * P + 2 * qq[k]) = make_uint2(b0, b1);
+		}
 	}
 	__syncthreads();
 
@@ -153,13 +171,16 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 			uint32_t h_cur = hmax(ra, c_cur, side_cur);
 			for (int sr = ra; sr < rb; sr++) {
 				const uint32_t h_next = hmax(sr + 1, c_next, side_next);
-				if (c_cur) {
-					const uint32_t m = fb_mx3(h_prev, h_next, side_cur);
+				// strict maximum per lane: c > m.  All values are < 2^15, so bit 15 of (c | 0x8000) - m - 1 is set iff c > m
+				// (no borrow crosses the lanes); a survivor is rare (under 3 % of the pixels), this test is not
+				const uint32_t m = fb_mx3(h_prev, h_next, side_cur);
+				const uint32_t gt = ((c_cur | 0x80008000u) - m - 0x00010001u) & 0x80008000u;
+				if (gt) {
 					const int y = y0 + sr - 1;
 #pragma unroll
 					for (int e = 0; e < 2; e++) {
-						const uint32_t v = (c_cur >> (16 * e)) & 0xFFFFu, mm = (m >> (16 * e)) & 0xFFFFu;
-						if (v > mm) {
+						if (gt & (0x8000u << (16 * e))) {
+							const uint32_t v = (c_cur >> (16 * e)) & 0xFFFFu;
 							const int x = 2 * j + 1 + e;
 							const uint32_t score = v + (uint32_t)g.fast_thr - 1u;
 							if (score_map) score_map[stream * (size_t)W * H + (size_t)(r0 + y) * W + c0 + x] = (uint8_t)score;
@@ -205,7 +226,7 @@ bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0)
 	return fb_smem_bytes(g, P, cap) <= 200 * 1024;
 }
 
-template <int THREADS>
+template <int THREADS, int PC>
 static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
 {
 	int P, cap;
@@ -214,22 +235,23 @@ static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &
 	int dev = 0;
 	cudaGetDevice(&dev);
 	if (dev < 64 && !attr_set[dev]) {
-		cudaError_t e = cudaFuncSetAttribute(lk_fast_band_kernel<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+		cudaError_t e = cudaFuncSetAttribute(lk_fast_band_kernel<THREADS, PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 		if (e != cudaSuccess) return e;
 		attr_set[dev] = true;
 	}
 	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
 	dim3 grid(LK_BINS * bands, n);
-	lk_fast_band_kernel<THREADS><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
+	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
 	return cudaGetLastError();
 }
 
 cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
 {
 	const int npc = g.bw / 2;
-	if (4 * npc <= 320) return fb_launch<320>(g, l0, s, n, score_map, st);
-	if (4 * npc <= 640) return fb_launch<640>(g, l0, s, n, score_map, st);
-	return fb_launch<1024>(g, l0, s, n, score_map, st);
+	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st);   // 640-px frames: pitch known at compile time
+	if (4 * npc <= 320) return fb_launch<320, 0>(g, l0, s, n, score_map, st);
+	if (4 * npc <= 640) return fb_launch<640, 0>(g, l0, s, n, score_map, st);
+	return fb_launch<1024, 0>(g, l0, s, n, score_map, st);
 }
 
 } // namespace aof
