@@ -225,6 +225,12 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 	int wy[3], wx[3];
 #pragma unroll
 	for (int k = 0; k < 3; k++) { const int idx = lane + 32 * k; wy[k] = idx / 9; wx[k] = idx - wy[k] * 9; }
+	// taps gathered by this lane: 12 x 12 template patch (i = lane + 32 k < 144), 10 x 10 window of J (i < 100)
+	int pr[5], pcol[5], jr[4], jc[4];
+#pragma unroll
+	for (int k = 0; k < 5; k++) { const int i = lane + 32 * k; pr[k] = i / 12; pcol[k] = i - pr[k] * 12; }
+#pragma unroll
+	for (int k = 0; k < 4; k++) { const int i = lane + 32 * k; jr[k] = i / 10; jc[k] = i - jr[k] * 10; }
 	for (int level = g.top; level >= 0; --level) {
 		const int w = g.w[level], h = g.h[level];
 		const uint8_t *I = prev.lvl[level] + stream * (size_t)w * h;
@@ -242,9 +248,16 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 		int w00, w01, w10, w11;
 		q14_weights(px - (float)ipx, py - (float)ipy, w00, w01, w10, w11);
 		__syncwarp();
-		for (int i = lane; i < 144; i += 32) {
-			const int r = i / 12, c = i - r * 12;
-			sc.I[i] = I[(size_t)reflect101(ipy - 1 + r, h) * w + reflect101(ipx - 1 + c, w)];
+		if (ipx >= 1 && ipx + 10 < w && ipy >= 1 && ipy + 10 < h) { // the patch is inside the image: no border arithmetic
+			const uint8_t *base = I + (size_t)(ipy - 1) * w + (ipx - 1);
+#pragma unroll
+			for (int k = 0; k < 5; k++)
+				if (lane + 32 * k < 144) sc.I[lane + 32 * k] = __ldg(base + pr[k] * w + pcol[k]);
+		} else {
+#pragma unroll
+			for (int k = 0; k < 5; k++)
+				if (lane + 32 * k < 144)
+					sc.I[lane + 32 * k] = I[(size_t)reflect101(ipy - 1 + pr[k], h) * w + reflect101(ipx - 1 + pcol[k], w)];
 		}
 		__syncwarp();
 		for (int i = lane; i < 100; i += 32) {
@@ -300,9 +313,16 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 			}
 			q14_weights(cx - (float)inx, cy - (float)iny, w00, w01, w10, w11);
 			__syncwarp();
-			for (int i = lane; i < 100; i += 32) {
-				const int r = i / 10, c = i - r * 10;
-				sc.J[i] = __ldg(&J[(size_t)reflect101(iny + r, h) * w + reflect101(inx + c, w)]);
+			if (inx >= 0 && inx + 9 < w && iny >= 0 && iny + 9 < h) {
+				const uint8_t *base = J + (size_t)iny * w + inx;
+#pragma unroll
+				for (int k = 0; k < 4; k++)
+					if (lane + 32 * k < 100) sc.J[lane + 32 * k] = __ldg(base + jr[k] * w + jc[k]);
+			} else {
+#pragma unroll
+				for (int k = 0; k < 4; k++)
+					if (lane + 32 * k < 100)
+						sc.J[lane + 32 * k] = __ldg(&J[(size_t)reflect101(iny + jr[k], h) * w + reflect101(inx + jc[k], w)]);
 			}
 			__syncwarp();
 			int p1 = 0, p2 = 0;
@@ -336,7 +356,7 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 #endif
 constexpr int TU_WARPS = AOF_TU_WARPS;
 
-__global__ void __launch_bounds__(TU_WARPS * 32)
+__global__ void __launch_bounds__(TU_WARPS * 32, 4) // 4 CTAs per SM: 512 streams are one wave
 lk_track_update_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev)
 {
 	__shared__ LkWarpScratch s_sc[TU_WARPS];
@@ -637,6 +657,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 	__shared__ int s_px[LK_BINS][SEL_MAX_TPB], s_py[LK_BINS][SEL_MAX_TPB];
 	__shared__ int s_gx[SEL_MAX_GOOD], s_gy[SEL_MAX_GOOD];
 	__shared__ unsigned long long s_red[SEL_THREADS / 32];
+	__shared__ int s_bx[SEL_THREADS / 32][LK_MAX_FEATURES], s_by[SEL_THREADS / 32][LK_MAX_FEATURES]; // per-warp: active points near the bin
 	const size_t stream = blockIdx.x;
 	const int N = g.n_feat, W = g.w[0];
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -677,6 +698,22 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 			const int needed = s_needed[b], cnt = s_cnt[b];
 			const int c0 = (b >> 2) * g.bw, r0 = (b & 3) * g.bh;
 			const uint32_t *list = s.kp + (stream * LK_BINS + b) * (size_t)g.kp_cap;
+			// only the active points whose exclusion square reaches into this bin can reject one of its keypoints
+			// (about a third of them for 4 x 4 bins and dist = half a bin): compact them once per bin
+			int nexb = 0;
+			for (int j0 = 0; j0 < nex; j0 += 32) {
+				const int j = j0 + lane;
+				const int ex = j < nex ? s_ex[j] : 0, ey = j < nex ? s_ey[j] : 0;
+				const bool near = j < nex && ex > c0 - g.dist && ex < c0 + g.bw - 1 + g.dist && ey > r0 - g.dist &&
+						  ey < r0 + g.bh - 1 + g.dist;
+				const uint32_t m = __ballot_sync(0xFFFFFFFFu, near);
+				if (near) {
+					const int k = nexb + __popc(m & ((1u << lane) - 1u));
+					s_bx[warp][k] = ex; s_by[warp][k] = ey;
+				}
+				nexb += __popc(m);
+			}
+			__syncwarp();
 			int npick = 0;
 			while (npick < needed) {
 				uint32_t best = 0;
@@ -687,7 +724,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 					if (key <= best) continue;
 					const int y = r0 + li / g.bw, x = c0 + li % g.bw;
 					bool ok = true;
-					for (int j = 0; j < nex && ok; j++) ok = !cheb_close(s_ex[j], s_ey[j], x, y, g.dist);
+					for (int j = 0; j < nexb && ok; j++) ok = !cheb_close(s_bx[warp][j], s_by[warp][j], x, y, g.dist);
 					for (int j = 0; j < npick && ok; j++) ok = !cheb_close(s_px[b][j], s_py[b][j], x, y, g.dist);
 					if (ok) best = key;
 				}
