@@ -37,7 +37,10 @@ SAD_INSTR_PER_PAIR = 40550                       # packed-byte instructions of t
 LK_STREAMS, LK_W, LK_H, LK_FEATURES, LK_ROT = 512, 640, 480, 20, 4
 LK_LEVEL_PX = [640 * 480, 320 * 240, 160 * 120, 80 * 60]
 LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read once + L1..L3 written = 408 000 B
-LK_FAST_OPS_PER_PIXEL_PAIR = 88                             # 16 ring differences + 72 packed min/max
+# FAST response per pixel pair: 16 ring differences + 50 two-input + 22 three-input packed min/max.  IADD and the two-input
+# VIMNMX.U16x2 issue on BOTH integer pipes (125 lanes/clk/SM measured, profiles/r1g_ubench_int_pipes.jsonl), VIMNMX3 only on
+# the ALU pipe (63): in ALU-pipe slots that is (16 + 50) / 2 + 22 = 55 per pair with a perfect split over the two pipes.
+LK_FAST_OPS_PER_PIXEL_PAIR = 55
 
 
 def peaks():
@@ -466,7 +469,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     alg_bytes = {"lk_pyr_down_kernel": n * (px0 + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0,
                  "lk_pyr_fused_kernel": n * LK_BYTES_PER_PAIR,      # level 0 read once + levels 1..3 written
                  "lk_fast_kernel": n * px0}                          # level 0 of the bins that need features
-    # FAST response: 16 differences + 72 packed min/max (the arc-pair network) per PAIR of pixels, every pixel scored
+    # FAST response (the arc-pair network) per PAIR of pixels, every pixel scored, in ALU-pipe slots (see the constant)
     alg_alu = {"lk_fast_kernel": n * (px0 / 2.0) * LK_FAST_OPS_PER_PIXEL_PAIR}
     kroof = {}
     for kname, kv in kb.items():
@@ -478,7 +481,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
                         "algorithmic_bytes_per_launch": alg_bytes[kname]}
         if kname in alg_alu and "alu_packed_instr_per_s" in pk:
             a = alg_alu[kname] / (k_ms * 1e-3)
-            e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed u16x2 instr/s",
+            e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "ALU-pipe slots/s (two-input packed min/max and IADD count 1/2: they issue on both integer pipes)",
                             "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_launch": alg_alu[kname]}
         e["bound"] = {"lk_pyr_fused_kernel": "hbm", "lk_pyr_down_kernel": "hbm", "lk_fast_kernel": "int-alu"}.get(kname, "latency")
         kroof[kname] = e

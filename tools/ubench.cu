@@ -6,7 +6,7 @@
 #include <cuda_runtime.h>
 
 #define ITERS 4096
-#define UNROLL 8  // independent chains per thread
+#define UNROLL 12 // independent chains per thread
 
 template <int OP> __global__ void __launch_bounds__(1024) k(uint32_t *out, uint32_t seed)
 {
@@ -30,6 +30,26 @@ template <int OP> __global__ void __launch_bounds__(1024) k(uint32_t *out, uint3
 				else asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(a[i]) : "r"(b), "r"(c));
 			}
 			if (OP == 7) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+			if (OP == 8) asm volatile("dp4a.u32.u32 %0, %1, %2, %0;" : "+r"(a[i]) : "r"(b), "r"(c));
+			if (OP == 9) { // 1 DP4A : 1 PRMT (different pipes?)
+				if (i & 1) asm volatile("prmt.b32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c & 0x7777));
+				else asm volatile("dp4a.u32.u32 %0, %1, %2, %0;" : "+r"(a[i]) : "r"(b), "r"(c));
+			}
+			if (OP == 10) { // 1 DP4A : 1 IMAD (same pipe?)
+				if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+				else asm volatile("dp4a.u32.u32 %0, %1, %2, %0;" : "+r"(a[i]) : "r"(b), "r"(c));
+			}
+			if (OP == 11) asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+			if (OP == 13) a[i] = __vimax3_u16x2(a[i], b, c + i);
+			if (OP == 14) { // 2 VIMNMX : 1 VIMNMX3 (the FAST network's mix)
+				if (i % 3 == 2) a[i] = __vimax3_u16x2(a[i], b, c + i);
+				else asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+			}
+			if (OP == 15) { // 1 VIMNMX : 1 IMAD
+				if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+				else asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+			}
+			if (OP == 12) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
 		}
 	}
 	uint32_t s = 0;
@@ -74,5 +94,13 @@ int main()
 	run<5>("vabsdiff4+imad 1:1", p.multiProcessorCount, clk, d);
 	run<6>("vabsdiff4+prmt 3:1", p.multiProcessorCount, clk, d);
 	run<7>("iadd", p.multiProcessorCount, clk, d);
+	run<8>("dp4a", p.multiProcessorCount, clk, d);
+	run<9>("dp4a+prmt 1:1", p.multiProcessorCount, clk, d);
+	run<10>("dp4a+imad 1:1", p.multiProcessorCount, clk, d);
+	run<11>("vimnmx.u16x2", p.multiProcessorCount, clk, d);
+	run<12>("imad.hi", p.multiProcessorCount, clk, d);
+	run<13>("vimnmx3.u16x2", p.multiProcessorCount, clk, d);
+	run<14>("vimnmx+vimnmx3 2:1", p.multiProcessorCount, clk, d);
+	run<15>("vimnmx+imad 1:1", p.multiProcessorCount, clk, d);
 	return 0;
 }
