@@ -93,7 +93,8 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	const size_t stream = blockIdx.y;
 	const int bin = blockIdx.x / bands, band = blockIdx.x - bin * bands;
 	if (!score_map && s.bin_needed[stream * LK_BINS + bin] == 0) return;
-	const int W = g.w[0], H = g.h[0], bw = g.bw, bh = g.bh;
+	const int W = g.w[0], H = g.h[0], bh = g.bh;
+	const int bw = PC ? (PC - 4) * 2 : g.bw;                      // compile-time bin width: the index arithmetic below folds
 	const int npc = bw >> 1, nq = bw >> 2;
 	const int c0 = (bin >> 2) * bw, r0 = (bin & 3) * bh;        // bin = x * 4 + y
 	const int y0 = 3 + band * FB_ROWS;                            // first output row of the band (bin coordinates)
@@ -165,33 +166,37 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 			side = fb_mx(lm, rm);
 			return fb_mx3(lm, c, rm);
 		};
-		if (ra < rb) {
-			uint32_t c_prev, c_cur, c_next, side_prev, side_cur, side_next;
-			uint32_t h_prev = hmax(ra - 1, c_prev, side_prev);
-			uint32_t h_cur = hmax(ra, c_cur, side_cur);
-			for (int sr = ra; sr < rb; sr++) {
+		// Rows are walked 16 at a time.  The strict-maximum bits of a row (bit 15 / bit 31 of the packed test) are shifted
+		// into a per-thread mask instead of being acted on: a warp almost always holds SOME survivor, so a branch per
+		// row would run its body for every row with one or two lanes active.  The mask is drained after the walk.
+		for (int r16 = ra; r16 < rb; r16 += 16) {
+			const int re = min(r16 + 16, rb);
+			uint32_t c_cur, c_next, side_cur, side_next, c_skip, side_skip;
+			uint32_t h_prev = hmax(r16 - 1, c_skip, side_skip);
+			uint32_t h_cur = hmax(r16, c_cur, side_cur);
+			uint32_t acc = 0u;
+			for (int sr = r16; sr < re; sr++) {
 				const uint32_t h_next = hmax(sr + 1, c_next, side_next);
 				// strict maximum per lane: c > m.  All values are < 2^15, so bit 15 of (c | 0x8000) - m - 1 is set iff c > m
-				// (no borrow crosses the lanes); a survivor is rare (under 3 % of the pixels), this test is not
+				// (no borrow crosses the lanes)
 				const uint32_t m = fb_mx3(h_prev, h_next, side_cur);
-				const uint32_t gt = ((c_cur | 0x80008000u) - m - 0x00010001u) & 0x80008000u;
-				if (gt) {
-					const int y = y0 + sr - 1;
-#pragma unroll
-					for (int e = 0; e < 2; e++) {
-						if (gt & (0x8000u << (16 * e))) {
-							const uint32_t v = (c_cur >> (16 * e)) & 0xFFFFu;
-							const int x = 2 * j + 1 + e;
-							const uint32_t score = v + (uint32_t)g.fast_thr - 1u;
-							if (score_map) score_map[stream * (size_t)W * H + (size_t)(r0 + y) * W + c0 + x] = (uint8_t)score;
-							else {
-								const int slot = atomicAdd(&s_n, 1);
-								if (slot < list_cap) sL[slot] = (score << 24) | (uint32_t)(y * bw + x);
-							}
-						}
-					}
-				}
+				acc = (acc >> 1) | (((c_cur | 0x80008000u) - m - 0x00010001u) & 0x80008000u);
 				h_prev = h_cur; h_cur = h_next; c_cur = c_next; side_cur = side_next;
+			}
+			// row r16 + i sits at bit 16 e + 15 - (n - 1 - i)
+			const int n = re - r16;
+			while (acc) {
+				const int p = __ffs((int)acc) - 1;
+				acc &= acc - 1u;
+				const int e = p >> 4, sr = r16 + n - 16 + (p & 15);
+				const uint32_t v = (col[sr * P] >> (16 * e)) & 0xFFFFu;
+				const int y = y0 + sr - 1, x = 2 * j + 1 + e;
+				const uint32_t score = v + (uint32_t)g.fast_thr - 1u;
+				if (score_map) score_map[stream * (size_t)W * H + (size_t)(r0 + y) * W + c0 + x] = (uint8_t)score;
+				else {
+					const int slot = atomicAdd(&s_n, 1);
+					if (slot < list_cap) sL[slot] = (score << 24) | (uint32_t)(y * bw + x);
+				}
 			}
 		}
 	}
