@@ -39,15 +39,18 @@ __device__ __forceinline__ uint32_t fb_mn3(uint32_t a, uint32_t b, uint32_t c) {
 __device__ __forceinline__ uint32_t fb_mx3(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
 
 // response + 257 per lane of the pixel pair whose centre is B[0][0] (A, B point at the centre row / pair column,
-// P = row pitch in words).  Materialised min3 / max3 only (ptxas 12.9 mis-folds max(m, -x), tools/ptxas_vimnmx3_neg_repro.cu).
+// P = row pitch in words).  The network runs on the ring values v_k themselves: min / max commute with the order-
+// reversing map D = c + 256 - v, so with X = max over arcs of min9(v) and Y = min over arcs of max9(v) the dark response
+// (+257) is c + 256 - Y and the bright one X + 256 - c: no per-tap subtraction.
+// Materialised min3 / max3 only (ptxas 12.9 mis-folds max(m, -x), tools/ptxas_vimnmx3_neg_repro.cu).
 __device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint32_t *B, int P)
 {
 	const uint32_t cb = B[0] + 0x01000100u;
 	uint32_t D[16];
-	D[0] = cb - B[3 * P];       D[1] = cb - A[3 * P + 1];   D[2] = cb - B[2 * P + 1];   D[3] = cb - A[P + 2];
-	D[4] = cb - A[2];           D[5] = cb - A[-P + 2];      D[6] = cb - B[-2 * P + 1];  D[7] = cb - A[-3 * P + 1];
-	D[8] = cb - B[-3 * P];      D[9] = cb - A[-3 * P];      D[10] = cb - B[-2 * P - 1]; D[11] = cb - A[-P - 1];
-	D[12] = cb - A[-1];         D[13] = cb - A[P - 1];      D[14] = cb - B[2 * P - 1];  D[15] = cb - A[3 * P];
+	D[0] = B[3 * P];       D[1] = A[3 * P + 1];   D[2] = B[2 * P + 1];   D[3] = A[P + 2];
+	D[4] = A[2];           D[5] = A[-P + 2];      D[6] = B[-2 * P + 1];  D[7] = A[-3 * P + 1];
+	D[8] = B[-3 * P];      D[9] = A[-3 * P];      D[10] = B[-2 * P - 1]; D[11] = A[-P - 1];
+	D[12] = A[-1];         D[13] = A[P - 1];      D[14] = B[2 * P - 1];  D[15] = A[3 * P];
 	uint32_t p[8], q[8], Pm[8], Qm[8];
 #pragma unroll
 	for (int j = 0; j < 8; j++) {
@@ -64,21 +67,21 @@ __device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint3
 	for (int i = 0; i < 8; i++) {
 		const uint32_t hi = fb_mx(D[2 * i], D[(2 * i + 9) & 15]);
 		const uint32_t lo = fb_mn(D[2 * i], D[(2 * i + 9) & 15]);
-		r[i] = fb_mn3(q[i], q[(i + 2) & 7], hi);    // best of the dark arcs starting at 2i and 2i + 1
-		R[i] = fb_mx3(Qm[i], Qm[(i + 2) & 7], lo);  // best of the bright arcs
+		r[i] = fb_mn3(q[i], q[(i + 2) & 7], hi);    // min9 of the better of the arcs starting at 2i and 2i + 1
+		R[i] = fb_mx3(Qm[i], Qm[(i + 2) & 7], lo);  // max9 likewise
 	}
-	uint32_t dark = fb_mx3(r[0], r[1], r[2]), bright = fb_mn3(R[0], R[1], R[2]);
-	dark = fb_mx3(dark, r[3], r[4]); bright = fb_mn3(bright, R[3], R[4]);
-	dark = fb_mx3(dark, r[5], r[6]); bright = fb_mn3(bright, R[5], R[6]);
-	dark = fb_mx(dark, r[7]); bright = fb_mn(bright, R[7]);
-	return fb_mx(dark, 0x02000200u - bright);
+	uint32_t X = fb_mx3(r[0], r[1], r[2]), Y = fb_mn3(R[0], R[1], R[2]);
+	X = fb_mx3(X, r[3], r[4]); Y = fb_mn3(Y, R[3], R[4]);
+	X = fb_mx3(X, r[5], r[6]); Y = fb_mn3(Y, R[5], R[6]);
+	X = fb_mx(X, r[7]); Y = fb_mn(Y, R[7]);
+	return fb_mx(cb - Y, X + 0x02000200u - cb);
 }
 
 // dynamic shared memory: A[FB_PROWS][P], B[FB_PROWS][P], responses[FB_SROWS][P], survivor list
 // PC = row pitch of the shared-memory arrays in words when it is known at compile time (84 for the 160-px bins of a
 // 640-px frame: every ring tap is then an immediate offset of one base address), 0 = run time (P_rt)
 template <int THREADS, int PC>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
 		    int list_cap)
 {
@@ -108,20 +111,27 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	const int n_prow = y1 - y0 + 8;
 	{
 		constexpr int LD_ROUNDS = 6;
+		// with a compile-time bin width that divides THREADS a thread keeps its word column and steps whole rows
+		constexpr bool FIXED_Q = PC != 0 && THREADS % (PC ? (PC - 4) / 2 : 1) == 0;
 		const int dt = THREADS / nq, dq = THREADS - dt * nq;      // (row, word) step of one round
 		int t = tid / nq, q = tid - t * nq;
 		uint32_t w0[LD_ROUNDS], w1[LD_ROUNDS];
 		int tt[LD_ROUNDS], qq[LD_ROUNDS];
+		const uint32_t *img32 = reinterpret_cast<const uint32_t *>(img);
+		const int W4 = W >> 2;
 #pragma unroll
 		for (int k = 0; k < LD_ROUNDS; k++) {
 			const int y = y0 - 4 + t;
 			const bool on = t < n_prow && y >= 0 && y < bh;       // rows -1 and bh only feed responses that are not computed
 			tt[k] = on ? t : -1; qq[k] = q;
-			const uint32_t *row = reinterpret_cast<const uint32_t *>(img + (size_t)(on ? y : 0) * W);
+			const uint32_t *row = img32 + (on ? y * W4 : 0);      // 32-bit offsets: a bin is far below 2^31 bytes
 			w0[k] = __ldg(row + q);
 			w1[k] = __ldg(row + (q + 1 < nq ? q + 1 : q));        // p[bw] is never used
-			t += dt; q += dq;
-			if (q >= nq) { q -= nq; t++; }
+			t += dt;
+			if (!FIXED_Q) {
+				q += dq;
+				if (q >= nq) { q -= nq; t++; }
+			}
 		}
 #pragma unroll
 		for (int k = 0; k < LD_ROUNDS; k++) {
@@ -141,12 +151,14 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	const int n_srow = y1 - y0 + 2;
 	const uint32_t lim = (256u + (uint32_t)g.fast_thr) * 0x00010001u;
 	if (grp < ngrp) {
+		// rows of the band whose response exists (3 <= y < bh - 3); the others (first / last band only) are zero.
+		// Columns outside [1, npc - 3] run the network on the pitch padding and drop the result.
+		const int sr_lo = max(0, 4 - y0), sr_hi = min(n_srow, bh - 2 - y0);
 		for (int sr = grp; sr < n_srow; sr += ngrp) {
-			const int y = y0 - 1 + sr;
 			uint32_t b = 0u;
-			if (col_ok && y >= 3 && y < bh - 3) {
+			if (sr >= sr_lo && sr < sr_hi) {
 				const uint32_t m = fb_score_pair(sA + (sr + 3) * P + j, sB + (sr + 3) * P + j, P);
-				b = fb_mx(m, lim) - lim;
+				b = col_ok ? fb_mx(m, lim) - lim : 0u;
 			}
 			sS[sr * P + j] = b;
 		}
