@@ -110,7 +110,7 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	// THREADS >= 8 nq, so 6 rounds cover the FB_PROWS x nq words; all loads of a thread are issued before the first use
 	const int n_prow = y1 - y0 + 8;
 	{
-		constexpr int LD_ROUNDS = 6;
+		constexpr int LD_ROUNDS = PC ? (FB_PROWS * ((PC - 4) / 2) + THREADS - 1) / THREADS : 6;
 		// with a compile-time bin width that divides THREADS a thread keeps its word column and steps whole rows
 		constexpr bool FIXED_Q = PC != 0 && THREADS % (PC ? (PC - 4) / 2 : 1) == 0;
 		const int dt = THREADS / nq, dq = THREADS - dt * nq;      // (row, word) step of one round
@@ -265,7 +265,9 @@ static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &
 cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
 {
 	const int npc = g.bw / 2;
-	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st);   // 640-px frames: pitch known at compile time
+	// 640-px frames: pitch known at compile time.  (640 threads per CTA was measured 24 % slower: 5 rows per thread do
+	// not amortise the per-thread set-up.)
+	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st);
 	if (4 * npc <= 320) return fb_launch<320, 0>(g, l0, s, n, score_map, st);
 	if (4 * npc <= 640) return fb_launch<640, 0>(g, l0, s, n, score_map, st);
 	return fb_launch<1024, 0>(g, l0, s, n, score_map, st);

@@ -37,10 +37,10 @@ SAD_INSTR_PER_PAIR = 40550                       # packed-byte instructions of t
 LK_STREAMS, LK_W, LK_H, LK_FEATURES, LK_ROT = 512, 640, 480, 20, 4
 LK_LEVEL_PX = [640 * 480, 320 * 240, 160 * 120, 80 * 60]
 LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read once + L1..L3 written = 408 000 B
-# FAST response per pixel pair: 16 ring differences + 50 two-input + 22 three-input packed min/max.  IADD and the two-input
-# VIMNMX.U16x2 issue on BOTH integer pipes (125 lanes/clk/SM measured, profiles/r1g_ubench_int_pipes.jsonl), VIMNMX3 only on
-# the ALU pipe (63): in ALU-pipe slots that is (16 + 50) / 2 + 22 = 55 per pair with a perfect split over the two pipes.
-LK_FAST_OPS_PER_PIXEL_PAIR = 55
+# FAST response per pixel pair: 50 two-input + 22 three-input packed min/max on the raw ring values.  The two-input
+# VIMNMX.U16x2 issues on BOTH integer pipes (125 lanes/clk/SM measured, profiles/r1g_ubench_int_pipes.jsonl), VIMNMX3 only on
+# the ALU pipe (63): in ALU-pipe slots that is 50 / 2 + 22 = 47 per pair with a perfect split over the two pipes.
+LK_FAST_OPS_PER_PIXEL_PAIR = 47
 
 
 def peaks():
