@@ -127,6 +127,9 @@ struct LkState {
 	int *target;            // [n]       targetNumPoints
 	int *kp_count;          // [n * 16]
 	uint32_t *kp;           // [n * 16 * kp_cap]  score << 24 | bin-local raster index
+	float2 *lk_next;        // [n * N]   LK result per slot, handed from the tracking CTAs to the bookkeeping CTA
+	uint8_t *lk_stat;       // [n * N]
+	int *ticket;            // [n]       tracking CTAs of the stream that have finished (0 between launches)
 };
 
 // camera model of setCameraMatrix / setCameraDistortion (flow_opencv.cpp:72-87); on only when both were set

@@ -54,6 +54,7 @@ static LkState state_from(const LkState &s, const LkGeom &g, size_t first)
 	v.prev_corners += first * N; v.prev_status += first * N; v.n_prev_corners += first; v.update_vec += first * N;
 	v.feat_cur += first * N; v.feat_prev += first * N; v.lim += first; v.bin_needed += first * LK_BINS; v.target += first;
 	v.kp_count += first * LK_BINS; v.kp += first * LK_BINS * (size_t)g.kp_cap;
+	v.lk_next += first * N; v.lk_stat += first * N; v.ticket += first;
 	return v;
 }
 
@@ -84,6 +85,7 @@ static int reset_state(aof_lk *h)
 	AOF_CUDA(cudaMemset(h->s.bin_needed, 0, sizeof(int) * LK_BINS * h->n));
 	AOF_CUDA(cudaMemset(h->s.target, 0, sizeof(int) * h->n));
 	AOF_CUDA(cudaMemset(h->s.kp_count, 0, sizeof(int) * LK_BINS * h->n));
+	AOF_CUDA(cudaMemset(h->s.ticket, 0, sizeof(int) * h->n));
 	h->have_prev = h->have_feat_prev = false;
 	h->cur = 0;
 	h->l0[0] = h->l0[1] = nullptr;
@@ -156,6 +158,9 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	    (e = cudaMalloc(&h->s.bin_needed, sizeof(int) * LK_BINS * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.target, sizeof(int) * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.kp_count, sizeof(int) * LK_BINS * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lk_next, sizeof(float2) * nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lk_stat, nN)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.ticket, sizeof(int) * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.kp, sizeof(uint32_t) * LK_BINS * (size_t)g.kp_cap * n_streams)) != cudaSuccess) {
 		set_error("aof_lk_create: %s", cudaGetErrorString(e));
 		aof_lk_destroy(h);
@@ -176,6 +181,7 @@ void aof_lk_destroy(aof_lk *h)
 	cudaFree(h->s.prev_corners); cudaFree(h->s.prev_status); cudaFree(h->s.n_prev_corners); cudaFree(h->s.update_vec);
 	cudaFree(h->s.feat_cur); cudaFree(h->s.feat_prev); cudaFree(h->s.lim); cudaFree(h->s.bin_needed);
 	cudaFree(h->s.target); cudaFree(h->s.kp_count); cudaFree(h->s.kp);
+	cudaFree(h->s.lk_next); cudaFree(h->s.lk_stat); cudaFree(h->s.ticket);
 	cudaFree(h->d_frames[0]); cudaFree(h->d_frames[1]);
 	cudaFreeHost(h->h_stage); cudaFreeHost(h->h_t); cudaFreeHost(h->h_out); cudaFreeHost(h->h_raw);
 	cudaFree(h->d_t); cudaFree(h->d_out); cudaFree(h->d_raw);

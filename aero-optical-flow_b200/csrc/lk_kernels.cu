@@ -10,6 +10,8 @@
 // Arithmetic spec: SURVEY.md Appendix A (verified bit-exact against cv2 4.13 by
 // oracle/lk_oracle.c, which these kernels must match bit for bit).  The file is
 // compiled with -fmad=false: every float operation rounds as written.
+#include <cstdlib>
+
 #include "aof_common.cuh"
 #include "aof_internal.h"
 
@@ -423,12 +425,96 @@ lk_track_update_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_pre
 	if (threadIdx.x == 0) s.target[stream] = target;
 }
 
+// The same step with the points of a stream spread over several small CTAs (TS_WARPS points each, one per warp):
+// an LK point is a long chain of dependent gathers (up to 4 levels x 30 iterations), so the time of the CTA-per-stream
+// form is the time of the warp that drew the three slowest points.  Here every point is its own warp, the CTAs of all
+// streams share the SMs dynamically, and the LAST CTA of a stream to finish (ticket counter) does the bookkeeping.
+constexpr int TS_WARPS = 4;
+
+__global__ void __launch_bounds__(TS_WARPS * 32, 8)
+lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev, int groups)
+{
+	__shared__ LkWarpScratch s_sc[TS_WARPS];
+	__shared__ int s_per_bin[LK_BINS];
+	__shared__ int s_last;
+	const int stream_i = blockIdx.x / groups, grp = blockIdx.x - stream_i * groups;
+	const size_t stream = stream_i;
+	const int N = g.n_feat;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	float2 *pc = s.prev_corners + stream * N;
+	uint8_t *ps = s.prev_status + stream * N;
+	int *uv = s.update_vec + stream * N;
+	float2 *fc = s.feat_cur + stream * N;
+	float2 *lk_next = s.lk_next + stream * N;
+	uint8_t *lk_stat = s.lk_stat + stream * N;
+	const int npc = s.n_prev_corners[stream];
+	const bool do_lk = have_prev && npc > 0;
+	if (do_lk) {
+		// only slots that were active can influence anything downstream; the reference tracks
+		// the stale ones too (trackFeatures.cpp:98) but never reads them again before they are reassigned
+		const int f = grp * TS_WARPS + warp;
+		if (f < npc && uv[f] == 1) {
+			const float2 p = pc[f];
+			float ox, oy;
+			const int st = lk_track_point(g, prev, next, stream, p.x, p.y, s_sc[warp], ox, oy);
+			if (lane == 0) { lk_next[f] = make_float2(ox, oy); lk_stat[f] = (uint8_t)st; }
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		__threadfence();
+		s_last = atomicAdd(&s.ticket[stream], 1) == groups - 1;
+	}
+	if (threadIdx.x < LK_BINS) s_per_bin[threadIdx.x] = 0;
+	__syncthreads();
+	if (!s_last) return;
+	__threadfence();
+	if (threadIdx.x == 0) s.ticket[stream] = 0;
+	if (threadIdx.x < LK_BINS) s.kp_count[stream * LK_BINS + threadIdx.x] = 0;
+	// trackFeatures.cpp:77-125, one thread per slot; then the demand of initMorePoints (:144-183): bin = x * 4 + y
+	int wants = 0;
+	for (int i = threadIdx.x; i < N; i += blockDim.x) {
+		int status = uv[i];
+		int pst = status == 1;
+		float2 feat = make_float2(-100.f, -100.f);
+		float2 corner = pc[i];
+		if (do_lk && i < npc) {
+			if (pst) {
+				corner = __ldcg(lk_next + i);                 // written by other CTAs of this launch: read at L2
+				pc[i] = corner;
+				if (!__ldcg(lk_stat + i)) pst = 0;
+			}
+			if (pst) {
+				if (corner.x < 0.f || corner.x > (float)g.w[0] || corner.y < 0.f || corner.y > (float)g.h[0]) status = 0;
+				else { feat = corner; status = 1; }
+			} else if (status == 1) status = 0;
+		}
+		ps[i] = (uint8_t)pst;
+		uv[i] = status;
+		fc[i] = feat;
+		wants += status == 2;
+		if (i < npc && status == 1) {
+			const int bx = (int)__fdiv_rn(corner.x, (float)g.bw), by = (int)__fdiv_rn(corner.y, (float)g.bh);
+			if (bx < 4 && by < 4) atomicAdd(&s_per_bin[bx * 4 + by], 1);
+		}
+	}
+	const int target = __syncthreads_count(wants); // N <= blockDim.x: at most one slot per thread
+	if (threadIdx.x < LK_BINS)
+		s.bin_needed[stream * LK_BINS + threadIdx.x] = target ? max(0, g.tpb - s_per_bin[threadIdx.x]) : 0;
+	if (threadIdx.x == 0) s.target[stream] = target;
+}
+
 cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
 				   int have_prev, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
+	static const bool v1 = getenv("AOF_TRACK_V1") && getenv("AOF_TRACK_V1")[0] == '1';
 	KernelTimer kt(KID_LK_TRACK_UPDATE, st);
-	lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
+	if (v1) lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
+	else {
+		const int groups = (g.n_feat + TS_WARPS - 1) / TS_WARPS;
+		lk_track_split_kernel<<<n * groups, TS_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev, groups);
+	}
 	count_launch();
 	return cudaGetLastError();
 }
