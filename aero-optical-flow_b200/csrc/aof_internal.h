@@ -126,7 +126,7 @@ struct LkState {
 	int *bin_needed;        // [n * 16]  neededFeatures per bin (bin = x * 4 + y)
 	int *target;            // [n]       targetNumPoints
 	int *kp_count;          // [n * 16]
-	uint32_t *kp;           // [n * 16 * kp_cap]  score << 24 | bin-local raster index
+	uint32_t *kp;           // [n * 16 * kp_cap]  score << 24 | y << 12 | x (bin-local, so raster order == numeric order)
 	float2 *lk_next;        // [n * N]   LK result per slot, handed from the tracking CTAs to the bookkeeping CTA
 	uint8_t *lk_stat;       // [n * N]
 	int *ticket;            // [n]       tracking CTAs of the stream that have finished (0 between launches)

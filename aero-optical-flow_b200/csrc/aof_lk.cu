@@ -124,6 +124,11 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	LkGeom &g = h->g;
 	g.n_feat = N; g.bw = W / 4; g.bh = H / 4; g.tpb = tpb; g.dist = g.bw / tpb; g.fast_thr = 10;
 	g.kp_cap = ((g.bw + 1) / 2) * ((g.bh + 1) / 2);
+	if (g.bw > 4096 || g.bh > 4096) { // keypoint entries carry 12-bit bin-local coordinates
+		delete h;
+		set_error("frame %dx%d too large: bins above 4096 px", W, H);
+		return AOF_ERR_UNSUPPORTED;
+	}
 	// cv::buildOpticalFlowPyramid: stop when the next level would be <= the window
 	int lw = W, lh = H, level = 0;
 	g.w[0] = W; g.h[0] = H;

@@ -18,7 +18,7 @@
 //     preserved), as u16x2 in shared memory; the 3 x 3 non-maximum suppression walks down the
 //     band with the horizontal maxima of the previous / next row carried in registers;
 //   * survivors are collected in shared memory and appended to the bin's list with one global
-//     atomic per CTA.  Entry = score << 24 | bin-local raster index (order in the list is free:
+//     atomic per CTA.  Entry = score << 24 | y << 12 | x, bin-local (order in the list is free:
 //     the selection kernel uses the total order score desc, raster asc).
 // Needs bw % 4 == 0, W % 4 == 0, a 4-byte aligned batch and bw <= 512; other shapes use lk_fast_kernel.
 #include <cstdlib>
@@ -207,7 +207,7 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 				if (score_map) score_map[stream * (size_t)W * H + (size_t)(r0 + y) * W + c0 + x] = (uint8_t)score;
 				else {
 					const int slot = atomicAdd(&s_n, 1);
-					if (slot < list_cap) sL[slot] = (score << 24) | (uint32_t)(y * bw + x);
+					if (slot < list_cap) sL[slot] = (score << 24) | ((uint32_t)y << 12) | (uint32_t)x;
 				}
 			}
 		}

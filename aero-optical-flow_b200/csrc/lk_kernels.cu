@@ -666,7 +666,7 @@ lk_fast_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__r
 		else {
 			const int slot = atomicAdd(&s.kp_count[stream * LK_BINS + bin], 1);
 			if (slot < g.kp_cap)
-				s.kp[(stream * LK_BINS + bin) * (size_t)g.kp_cap + slot] = ((uint32_t)v << 24) | (uint32_t)(y * bw + x);
+				s.kp[(stream * LK_BINS + bin) * (size_t)g.kp_cap + slot] = ((uint32_t)v << 24) | ((uint32_t)y << 12) | (uint32_t)x;
 		}
 	}
 }
@@ -705,6 +705,7 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 constexpr int SEL_THREADS = AOF_SEL_THREADS;
 constexpr int SEL_MAX_TPB = (LK_MAX_FEATURES - 1) / LK_BINS + 1; // 7
 constexpr int SEL_MAX_GOOD = LK_BINS * SEL_MAX_TPB + LK_MAX_FEATURES;
+constexpr int SEL_STAGE = 8192 / (SEL_THREADS / 32);          // keypoints of a bin staged in shared memory (32 KB per CTA)
 
 __device__ __forceinline__ bool cheb_close(int ax, int ay, int bx, int by, int dist)
 {
@@ -744,6 +745,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 	__shared__ int s_gx[SEL_MAX_GOOD], s_gy[SEL_MAX_GOOD];
 	__shared__ unsigned long long s_red[SEL_THREADS / 32];
 	__shared__ int s_bx[SEL_THREADS / 32][LK_MAX_FEATURES], s_by[SEL_THREADS / 32][LK_MAX_FEATURES]; // per-warp: active points near the bin
+	__shared__ uint32_t s_key[SEL_THREADS / 32][SEL_STAGE];     // per-warp: keys of the bin's staged keypoints
 	const size_t stream = blockIdx.x;
 	const int N = g.n_feat, W = g.w[0];
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -800,25 +802,50 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 				nexb += __popc(m);
 			}
 			__syncwarp();
+			// The bin's keypoints are staged in shared memory once (the first SEL_STAGE of them; a bin of a 640 x 480 frame
+			// holds a few hundred), turned into keys (score desc, raster asc) and filtered against the active points: a
+			// keypoint rejected once stays rejected, so every pick is then one max over the keys and one pass that
+			// clears the keys inside the pick's exclusion square.  Entries beyond SEL_STAGE are tested from global memory.
+			uint32_t *key = s_key[warp];
+			const int cs = min(cnt, SEL_STAGE);
+#pragma unroll 4
+			for (int e = lane; e < cs; e += 32) key[e] = list[e];
+			__syncwarp();
+			for (int e = lane; e < cs; e += 32) {
+				const uint32_t v = key[e];
+				const int x = c0 + (int)(v & 0xFFFu), y = r0 + (int)((v >> 12) & 0xFFFu);
+				bool ok = true;
+				for (int j = 0; j < nexb && ok; j++) ok = !cheb_close(s_bx[warp][j], s_by[warp][j], x, y, g.dist);
+				key[e] = ok ? (v & 0xFF000000u) | (0xFFFFFFu - (v & 0xFFFFFFu)) : 0u;
+			}
+			__syncwarp();
 			int npick = 0;
 			while (npick < needed) {
 				uint32_t best = 0;
-				for (int e = lane; e < cnt; e += 32) {
+				for (int e = lane; e < cs; e += 32) best = max(best, key[e]);
+				for (int e = SEL_STAGE + lane; e < cnt; e += 32) {
 					const uint32_t v = list[e];
-					const int li = v & 0xFFFFFF;
-					const uint32_t key = (v & 0xFF000000u) | (0xFFFFFFu - li);
-					if (key <= best) continue;
-					const int y = r0 + li / g.bw, x = c0 + li % g.bw;
+					const uint32_t k = (v & 0xFF000000u) | (0xFFFFFFu - (v & 0xFFFFFFu));
+					if (k <= best) continue;
+					const int x = c0 + (int)(v & 0xFFFu), y = r0 + (int)((v >> 12) & 0xFFFu);
 					bool ok = true;
 					for (int j = 0; j < nexb && ok; j++) ok = !cheb_close(s_bx[warp][j], s_by[warp][j], x, y, g.dist);
 					for (int j = 0; j < npick && ok; j++) ok = !cheb_close(s_px[b][j], s_py[b][j], x, y, g.dist);
-					if (ok) best = key;
+					if (ok) best = k;
 				}
 				best = __reduce_max_sync(0xFFFFFFFFu, best);
 				if (!best) break;
-				const int li = 0xFFFFFF - (best & 0xFFFFFF);
-				if (lane == 0) { s_px[b][npick] = c0 + li % g.bw; s_py[b][npick] = r0 + li / g.bw; }
+				const uint32_t li = 0xFFFFFFu - (best & 0xFFFFFFu);
+				const int px = c0 + (int)(li & 0xFFFu), py = r0 + (int)(li >> 12);
+				if (lane == 0) { s_px[b][npick] = px; s_py[b][npick] = py; }
 				npick++;
+				if (npick < needed)
+					for (int e = lane; e < cs; e += 32) {
+						const uint32_t k = key[e];
+						if (!k) continue;
+						const uint32_t l2 = 0xFFFFFFu - (k & 0xFFFFFFu);
+						if (cheb_close(px, py, c0 + (int)(l2 & 0xFFFu), r0 + (int)(l2 >> 12), g.dist)) key[e] = 0u;
+					}
 				__syncwarp();
 			}
 			if (lane == 0) s_npick[b] = npick;
@@ -851,8 +878,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 				const uint32_t *list = s.kp + (stream * LK_BINS + b) * (size_t)g.kp_cap;
 				for (int e = tid; e < cnt; e += SEL_THREADS) {
 					const uint32_t v = list[e];
-					const int li = v & 0xFFFFFF;
-					const int y = r0 + li / g.bw, x = c0 + li % g.bw;
+					const int y = r0 + (int)((v >> 12) & 0xFFFu), x = c0 + (int)(v & 0xFFFu);
 					const unsigned long long key = ((unsigned long long)(v >> 24) << 32) | (0xFFFFFFFFu - (uint32_t)(y * W + x));
 					if (key <= best) continue;
 					bool ok = true;
