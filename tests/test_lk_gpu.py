@@ -224,3 +224,24 @@ def test_undistort_branch_matches_oracle(pkg):
         assert f.calc_flow(fr[k], 1000 + 9000 * k) == o.calc_flow(fr[k], 1000 + 9000 * k), k
         check_state(f.state(), 0, o.state())
     f.close()
+
+
+@pytest.mark.parametrize("w,h,nf", [(1280, 720, 40), (1024, 768, 100)])
+def test_large_frames_match_oracle(pkg, w, h, nf):
+    """Bins of 320 x 180 / 256 x 192 px hold more FAST survivors than the selection kernel stages in shared memory
+    (the tail is read from global memory), the banded FAST kernel runs its run-time-pitch form, 100 = the slot limit."""
+    n, T = 2, 4
+    seqs = [pkg.synth.lk_sequence(T, w, h, 3 - 5 * i, -2 + 3 * i, seed=700 + i) for i in range(n)]
+    f = pkg.LkFlow(FX, FY, -1, w, h, nf, n_streams=n)
+    orc = [olk.Tracker(FX, FY, -1, w, h, nf) for _ in range(n)]
+    for k in range(T):
+        t_us = np.full(n, 1000 + 20000 * k, np.uint32)
+        out, raw = f.calc_flow_batch(np.stack([s[k] for s in seqs]), t_us, want_raw=True)
+        gs = f.state()
+        for i in range(n):
+            q, dt, fx, fy = orc[i].calc_flow(seqs[i][k], int(t_us[i]))
+            os_ = orc[i].state()
+            assert out["quality"][i] == q and out["flow_x"][i] == np.float32(fx) and out["flow_y"][i] == np.float32(fy), (k, i)
+            assert (raw["inliers"][i], raw["fast_bins"][i], raw["active"][i]) == (os_["inliers"], os_["fast_bins"], os_["active"])
+            check_state(gs, i, os_)
+    f.close()
