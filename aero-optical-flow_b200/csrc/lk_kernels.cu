@@ -10,6 +10,7 @@
 // Arithmetic spec: SURVEY.md Appendix A (verified bit-exact against cv2 4.13 by
 // oracle/lk_oracle.c, which these kernels must match bit for bit).  The file is
 // compiled with -fmad=false: every float operation rounds as written.
+#include <climits>
 #include <cstdlib>
 
 #include "aof_common.cuh"
@@ -307,6 +308,7 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 		D = __fdiv_rn(1.f, D);
 		float cx = nx - half, cy = ny - half;
 		float pdx = 0.f, pdy = 0.f;
+		int win_x = INT_MIN, win_y = INT_MIN;                  // integer position of the window held in sc.J
 		for (int j = 0; j < 30; j++) {
 			const int inx = (int)floorf(cx), iny = (int)floorf(cy);
 			if (inx < -LK_WIN || inx >= w || iny < -LK_WIN || iny >= h) {
@@ -314,19 +316,25 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 				break;
 			}
 			q14_weights(cx - (float)inx, cy - (float)iny, w00, w01, w10, w11);
-			__syncwarp();
-			if (inx >= 0 && inx + 9 < w && iny >= 0 && iny + 9 < h) {
-				const uint8_t *base = J + (size_t)iny * w + inx;
+			// the 10 x 10 taps depend on the integer position only: after the first step or two the update is a fraction
+			// of a pixel and the window already in shared memory is the one needed (the gather is the one global
+			// round trip of an iteration)
+			if (inx != win_x || iny != win_y) {
+				win_x = inx; win_y = iny;
+				__syncwarp();
+				if (inx >= 0 && inx + 9 < w && iny >= 0 && iny + 9 < h) {
+					const uint8_t *base = J + (size_t)iny * w + inx;
 #pragma unroll
-				for (int k = 0; k < 4; k++)
-					if (lane + 32 * k < 100) sc.J[lane + 32 * k] = __ldg(base + jr[k] * w + jc[k]);
-			} else {
+					for (int k = 0; k < 4; k++)
+						if (lane + 32 * k < 100) sc.J[lane + 32 * k] = __ldg(base + jr[k] * w + jc[k]);
+				} else {
 #pragma unroll
-				for (int k = 0; k < 4; k++)
-					if (lane + 32 * k < 100)
-						sc.J[lane + 32 * k] = __ldg(&J[(size_t)reflect101(iny + jr[k], h) * w + reflect101(inx + jc[k], w)]);
+					for (int k = 0; k < 4; k++)
+						if (lane + 32 * k < 100)
+							sc.J[lane + 32 * k] = __ldg(&J[(size_t)reflect101(iny + jr[k], h) * w + reflect101(inx + jc[k], w)]);
+				}
+				__syncwarp();
 			}
-			__syncwarp();
 			int p1 = 0, p2 = 0;
 #pragma unroll
 			for (int k = 0; k < 3; k++)
@@ -429,9 +437,15 @@ lk_track_update_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_pre
 // an LK point is a long chain of dependent gathers (up to 4 levels x 30 iterations), so the time of the CTA-per-stream
 // form is the time of the warp that drew the three slowest points.  Here every point is its own warp, the CTAs of all
 // streams share the SMs dynamically, and the LAST CTA of a stream to finish (ticket counter) does the bookkeeping.
-constexpr int TS_WARPS = 4;
+#ifndef AOF_TS_WARPS
+#define AOF_TS_WARPS 4
+#endif
+#ifndef AOF_TS_MINB
+#define AOF_TS_MINB 8
+#endif
+constexpr int TS_WARPS = AOF_TS_WARPS;
 
-__global__ void __launch_bounds__(TS_WARPS * 32, 8)
+__global__ void __launch_bounds__(TS_WARPS * 32, AOF_TS_MINB)
 lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev, int groups)
 {
 	__shared__ LkWarpScratch s_sc[TS_WARPS];
