@@ -37,10 +37,10 @@ SAD_INSTR_PER_PAIR = 40550                       # packed-byte instructions of t
 LK_STREAMS, LK_W, LK_H, LK_FEATURES, LK_ROT = 512, 640, 480, 20, 4
 LK_LEVEL_PX = [640 * 480, 320 * 240, 160 * 120, 80 * 60]
 LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read once + L1..L3 written = 408 000 B
-# FAST response per pixel pair: 50 two-input + 22 three-input packed min/max on the raw ring values.  The two-input
-# VIMNMX.U16x2 issues on BOTH integer pipes (125 lanes/clk/SM measured, profiles/r1g_ubench_int_pipes.jsonl), VIMNMX3 only on
-# the ALU pipe (63): in ALU-pipe slots that is 50 / 2 + 22 = 47 per pair with a perfect split over the two pipes.
-LK_FAST_OPS_PER_PIXEL_PAIR = 47
+# FAST response per pixel pair: 72 packed min/max (50 VIMNMX.U16x2 + 22 VIMNMX3.U16x2) on the raw ring values, all on the
+# ALU pipe at 63 lanes/clk/SM (profiles/r1h_ubench_int_pipes.jsonl; the 125 of the earlier r1g file was ptxas fusing a chain
+# of max into VIMNMX3)
+LK_FAST_OPS_PER_PIXEL_PAIR = 72
 
 
 def peaks():
@@ -431,6 +431,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     sign = 1.0 if 1 <= p <= rot // 2 else -1.0     # the last step went forward or back along the triangle wave
     ok = (np.abs(raw["px_x"] - sign * vel[:, 0]) < 1e-2) & (np.abs(raw["px_y"] - sign * vel[:, 1]) < 1e-2) & (raw["inliers"] >= 5)
     assert ok.mean() > 0.97, "timed LK path does not recover the translations (%.3f ok)" % ok.mean()
+    bins_frac = float(raw["fast_bins"].mean()) / 16.0   # share of the 16 bins FAST ran on in the last timed step (steady state)
     kb = kernel_breakdown(pkg, step, k, min(args.steps, 50))
     k += min(args.steps, 50)
 
@@ -468,9 +469,9 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     px0 = LK_LEVEL_PX[0]
     alg_bytes = {"lk_pyr_down_kernel": n * (px0 + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0,
                  "lk_pyr_fused_kernel": n * LK_BYTES_PER_PAIR,      # level 0 read once + levels 1..3 written
-                 "lk_fast_kernel": n * px0}                          # level 0 of the bins that need features
-    # FAST response (the arc-pair network) per PAIR of pixels, every pixel scored, in ALU-pipe slots (see the constant)
-    alg_alu = {"lk_fast_kernel": n * (px0 / 2.0) * LK_FAST_OPS_PER_PIXEL_PAIR}
+                 "lk_fast_kernel": n * px0 * bins_frac}              # level 0 of the bins that need features
+    # FAST response (the arc-pair network) per PAIR of pixels, every pixel of a bin that needs features scored
+    alg_alu = {"lk_fast_kernel": n * (px0 / 2.0) * bins_frac * LK_FAST_OPS_PER_PIXEL_PAIR}
     kroof = {}
     for kname, kv in kb.items():
         k_ms = kv["ms_per_step"] / max(1.0, kv["launches_per_step"])
@@ -481,7 +482,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
                         "algorithmic_bytes_per_launch": alg_bytes[kname]}
         if kname in alg_alu and "alu_packed_instr_per_s" in pk:
             a = alg_alu[kname] / (k_ms * 1e-3)
-            e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "ALU-pipe slots/s (two-input packed min/max and IADD count 1/2: they issue on both integer pipes)",
+            e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed u16x2 min/max instr/s", "bins_scored_frac": bins_frac,
                             "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_launch": alg_alu[kname]}
         e["bound"] = {"lk_pyr_fused_kernel": "hbm", "lk_pyr_down_kernel": "hbm", "lk_fast_kernel": "int-alu"}.get(kname, "latency")
         kroof[kname] = e

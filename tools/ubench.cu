@@ -39,15 +39,21 @@ template <int OP> __global__ void __launch_bounds__(1024) k(uint32_t *out, uint3
 				if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
 				else asm volatile("dp4a.u32.u32 %0, %1, %2, %0;" : "+r"(a[i]) : "r"(b), "r"(c));
 			}
-			if (OP == 11) asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+			// max then min: a chain of max alone is fused by ptxas into VIMNMX3 (two source ops per instruction), which made
+			// the first version of this line read 125 lanes/clk; min(max(a, b), c) cannot be fused
+			if (OP == 11) {
+				asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				asm volatile("min.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+			}
 			if (OP == 13) a[i] = __vimax3_u16x2(a[i], b, c + i);
-			if (OP == 14) { // 2 VIMNMX : 1 VIMNMX3 (the FAST network's mix)
-				if (i % 3 == 2) a[i] = __vimax3_u16x2(a[i], b, c + i);
-				else asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+			if (OP == 14) { // 2 VIMNMX : 1 VIMNMX3 (the FAST network's mix), unfusable order
+				asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				asm volatile("min.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+				a[i] = __vimax3_u16x2(a[i], b, c + i);
 			}
 			if (OP == 15) { // 1 VIMNMX : 1 IMAD
-				if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
-				else asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				asm volatile("max.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
 			}
 			if (OP == 12) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
 		}
@@ -74,7 +80,7 @@ template <int OP> void run(const char *name, int sms, int clk_khz, uint32_t *d)
 		float ms; cudaEventElapsedTime(&ms, e0, e1);
 		if (ms < best) best = ms;
 	}
-	double ops = (double)blocks * threads * ITERS * UNROLL;
+	double ops = (double)blocks * threads * ITERS * UNROLL * (OP == 11 || OP == 15 ? 2 : OP == 14 ? 3 : 1);
 	double per_s = ops / (best * 1e-3);
 	printf("{\"op\": \"%s\", \"ms\": %.4f, \"thread_ops_per_s\": %.4e, \"lanes_per_clk_per_sm_at_max_clk\": %.2f}\n", name, best,
 	       per_s, per_s / sms / (clk_khz * 1e3));
@@ -97,7 +103,7 @@ int main()
 	run<8>("dp4a", p.multiProcessorCount, clk, d);
 	run<9>("dp4a+prmt 1:1", p.multiProcessorCount, clk, d);
 	run<10>("dp4a+imad 1:1", p.multiProcessorCount, clk, d);
-	run<11>("vimnmx.u16x2", p.multiProcessorCount, clk, d);
+	run<11>("vimnmx.u16x2 (max,min alternating)", p.multiProcessorCount, clk, d);
 	run<12>("imad.hi", p.multiProcessorCount, clk, d);
 	run<13>("vimnmx3.u16x2", p.multiProcessorCount, clk, d);
 	run<14>("vimnmx+vimnmx3 2:1", p.multiProcessorCount, clk, d);
