@@ -43,6 +43,16 @@ LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read onc
 LK_FAST_OPS_PER_PIXEL_PAIR = 72
 
 
+def ncu_traffic(kernel, n, n_ref):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json), scaled from the
+    capture's streams per launch (n_ref) to this run's; None when there is no capture."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return float(t[kernel]) * n / n_ref
+    except Exception:
+        return None
+
+
 def peaks():
     p = {"hbm_gbs": 6650.0, "which": "fallback"}
     try:
@@ -369,8 +379,8 @@ def run_sad_gpu(args, rank, world, local, with_cpu):
                          "current frame by construction of calcFlow" % (rot, rot * fb >> 20),
                    "parallelism": "streams sharded across ranks, host gather, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk["which"],
-                     "kernel": "sad_flow_kernel<4>", "kernel_ms": kern_ms, "dominant_kernel_by_time": dom,
+                     "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic("sad_flow_kernel", n, 4096),
+                     "peak_source": pk["which"], "kernel": "sad_flow_kernel<4>", "kernel_ms": kern_ms, "dominant_kernel_by_time": dom,
                      "algorithmic_bytes_per_launch": n * SAD_BYTES_PER_PAIR},
         "kernels": kb,
         "e2e": {"value": world * n * e_steps / (e2e_ms * 1e-3), "unit": "frame-pairs/s",
@@ -479,7 +489,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
         if kname in alg_bytes:
             a = alg_bytes[kname] / (k_ms * 1e-3) / 1e9
             e["hbm"] = {"achieved": a, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": a / pk["hbm_gbs"],
-                        "algorithmic_bytes_per_launch": alg_bytes[kname]}
+                        "algorithmic_bytes_per_launch": alg_bytes[kname], "traffic": ncu_traffic(kname, n, 512)}
         if kname in alg_alu and "alu_packed_instr_per_s" in pk:
             a = alg_alu[kname] / (k_ms * 1e-3)
             e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed u16x2 min/max instr/s", "bins_scored_frac": bins_frac,
@@ -497,7 +507,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
                    "l2": "frames rotate over %d buffers = %d MiB > 126 MB L2" % (rot, rot * fb >> 20),
                    "parallelism": "streams sharded across ranks, host gather, no collective"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk["which"],
+                     "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic(dom, n, 512), "peak_source": pk["which"],
                      "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
                      "note": "dominant kernel by time; its binding roofline is in kernel_rooflines[kernel][bound] "
                              "(lk_fast_kernel is integer-ALU bound, the HBM-bound kernel of the step is lk_pyr_fused_kernel)",
