@@ -365,6 +365,49 @@ def run_sad_gpu(args, rank, world, local, with_cpu):
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
     assert (res["quality"] == 255).mean() > 0.99
     flow_e.close(); flow.close()
+
+    # BASELINE config 1 as written: ONE 64x64 stream, host frame in, result out (latency, not throughput)
+    one = pkg.Px4Flow(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=1, device=local)
+    for k in range(4):
+        one.calc_flow(h_frames[k % rot, 0], 1000 * k)
+    t0 = time.perf_counter()
+    for k in range(100):
+        one.calc_flow(h_frames[(k + 4) % rot, 0], 1000 * (k + 4))
+    lat_us = (time.perf_counter() - t0) / 100 * 1e6
+    one.close()
+
+    # BASELINE config 4: dense block field of 1280x720 pairs, +-8 (device-resident pairs, 8 distinct pairs rotating)
+    dense = None
+    if rank == 0:
+        dn, dw, dh, ds = 8, 1280, 720, 8
+        rng = np.random.default_rng(77)
+        tex = pkg.synth.box_blur3(rng.integers(0, 256, (dh + 32, dw + 32), dtype=np.uint8))
+        shifts = rng.integers(-ds, ds + 1, (dn, 2))
+        d_prev = torch.from_numpy(np.stack([tex[16:16 + dh, 16:16 + dw]] * dn)).cuda()
+        d_cur = torch.from_numpy(np.stack([tex[16 - sy:16 - sy + dh, 16 - sx:16 - sx + dw] for sx, sy in shifts])).cuda()
+        df = pkg.SadDense(dw, dh, ds, 30, 3000, device=local)
+        d_field = torch.zeros((dn, df.nby, df.nbx, pkg.capi.dense_block_dtype.itemsize), dtype=torch.uint8, device="cuda")
+        run = lambda: df.compute_device(d_prev.data_ptr(), d_cur.data_ptr(), dn, d_field.data_ptr(), stream=stream)
+        for _ in range(3):
+            run()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        ev0.record()
+        reps = 20
+        for _ in range(reps):
+            run()
+        ev1.record()
+        torch.cuda.synchronize()
+        d_ms = ev0.elapsed_time(ev1) / reps
+        field = d_field.cpu().numpy().view(pkg.capi.dense_block_dtype).reshape(dn, df.nby, df.nbx)
+        hit = float(np.mean([((field[i]["dx"] == shifts[i, 0]) & (field[i]["dy"] == shifts[i, 1]) & (field[i]["flags"] == 3)).mean()
+                             for i in range(dn)]))
+        assert hit > 0.9, "dense SAD field does not recover the translations (%.3f)" % hit
+        blocks = df.nbx * df.nby
+        dense = {"workload": "dense_sad_1280x720_search8 (BASELINE config 4), %d pairs per launch" % dn, "pairs_per_s": dn / (d_ms * 1e-3),
+                 "ms_per_pair": d_ms / dn, "blocks_per_pair": blocks, "translation_recovered_frac": float(hit),
+                 "l2": "8 pairs = 14.7 MB: L2-resident, the kernel is integer-ALU bound by 6x (SURVEY 8d)"}
+        df.close()
     if rank != 0:
         return None
     pk = peaks()
@@ -394,6 +437,13 @@ def run_sad_gpu(args, rank, world, local, with_cpu):
                                  "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
                                  "frac": a / pk["alu_packed_instr_per_s"], "peak_source": pk["alu_which"],
                                  "algorithmic_instr_per_pair": SAD_INSTR_PER_PAIR}
+    r["single_stream_latency_us"] = lat_us
+    if dense is not None:
+        if "alu_packed_instr_per_s" in pk:
+            a = dense["blocks_per_pair"] * 4944.0 * dense["pairs_per_s"]     # 289 x 16 SAD + 320 sub-pixel instr per block
+            dense["roofline_int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
+                                         "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_block": 4944}
+        r["dense"] = dense
     if with_cpu:
         r["cpu_baseline"] = cpu_sad(frames, 10.0)
     return r
@@ -563,7 +613,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": p["dtype"], "data": "synthetic", "config": p["config"], "roofline": p["roofline"],
             "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
-    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu", "kernel_rooflines"):
+    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu", "kernel_rooflines", "dense"):
         if key in p:
             line[key] = p[key]
     if args.workload == "both":
