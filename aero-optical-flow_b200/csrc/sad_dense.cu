@@ -7,7 +7,7 @@
 // assumes a square image); a block is computed when its search window plus
 // the 1-px sub-pixel halo lies inside the image.
 //
-// CTA = 8 x 4 blocks.  Their 64 x 32 reference pixels and the (64 + 24) x (32 + 2S + 2) search
+// CTA = 8 x 2 blocks.  Their 64 x 16 reference pixels and the (64 + 24) x (16 + 2S + 2) search
 // region of the current frame are staged in shared memory with coalesced 32-bit loads; then the
 // phases of sad_flow_kernel: texture gate, thread = (block, x-displacement) sliding search with
 // one byte-alignment per row shared by all y-displacements, packed-key arg-min, half-pixel
@@ -18,9 +18,10 @@
 namespace aof {
 
 #ifndef DENSE_MINB
-#define DENSE_MINB 3   // 3 CTAs per SM (registers capped at 40): measured 11 % faster than 2 on B200
+#define DENSE_MINB 5   // CTAs per SM (40 registers, no spill).  Measured on B200, 1280x720 +-8: 8x4-block CTAs at 2 / 3 per SM
+                       // 105 k / 127 k pairs/s, 8x2-block CTAs at 5 per SM 133 k: more, smaller CTAs overlap their phases better
 #endif
-constexpr int DN_BX = 8, DN_BY = 4, DN_BLOCKS = DN_BX * DN_BY;
+constexpr int DN_BX = 8, DN_BY = 2, DN_BLOCKS = DN_BX * DN_BY;
 constexpr int DN_MARGIN = 12;                       // columns left of the tile in smem (>= S + 1, multiple of 4)
 constexpr int DN_CP = DN_BX * 8 + 2 * DN_MARGIN;    // pitch of the current-frame tile: 88 bytes
 constexpr int DN_PP = DN_BX * 8;                    // pitch of the reference tile: 64 bytes
