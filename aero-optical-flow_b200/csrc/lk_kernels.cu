@@ -212,7 +212,10 @@ __device__ __forceinline__ float warp_sum_exact_f32(int v)
 {
 	const int lo = __reduce_add_sync(0xFFFFFFFFu, v & 0xFFFF);
 	const int hi = __reduce_add_sync(0xFFFFFFFFu, v >> 16);
-	return __ll2float_rn(((long long)hi << 16) + lo);
+	const long long t = ((long long)hi << 16) + lo;
+	// same rounding either way; the 32-bit conversion is an ALU instruction, the 64-bit one a slow XU one on the
+	// critical path of every LK iteration (the total almost always fits)
+	return t == (long long)(int)t ? (float)(int)t : __ll2float_rn(t);
 }
 
 // returns status (1/0); next point in (nx, ny).  All lanes run the same scalar math.
@@ -347,8 +350,17 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 			const float ddx = (A12 * b2 - A22 * b1) * D, ddy = (A12 * b1 - A11 * b2) * D;
 			cx += ddx; cy += ddy;
 			nx = cx + half; ny = cy + half;
-			if ((double)ddx * (double)ddx + (double)ddy * (double)ddy <= 0.01 * 0.01) break;
-			if (j > 0 && (double)fabsf(ddx + pdx) < 0.01 && (double)fabsf(ddy + pdy) < 0.01) {
+			// delta.ddot(delta) <= epsilon^2 is evaluated in double by the reference.  The f32 value of the same sum is
+			// within 2e-7 relative of it, so only a result that close to the threshold needs the double arithmetic
+			// (which is a chain of slow FP64 instructions on the critical path of every iteration).
+			const float dd32 = ddx * ddx + ddy * ddy;
+			bool small;
+			if (dd32 < 9.9999e-5f) small = true;
+			else if (dd32 > 1.00001e-4f) small = false;
+			else small = (double)ddx * (double)ddx + (double)ddy * (double)ddy <= 0.01 * 0.01;
+			if (small) break;
+			// (double)f < 0.01 for an f32 f is f <= 0.01f: 0.01f is the largest f32 below the double 0.01
+			if (j > 0 && fabsf(ddx + pdx) <= 0.01f && fabsf(ddy + pdy) <= 0.01f) {
 				nx -= ddx * 0.5f; ny -= ddy * 0.5f;
 				break;
 			}
