@@ -483,7 +483,7 @@ lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev
 			const float2 p = pc[f];
 			float ox, oy;
 			const int st = lk_track_point(g, prev, next, stream, p.x, p.y, s_sc[warp], ox, oy);
-			if (lane == 0) { lk_next[f] = make_float2(ox, oy); lk_stat[f] = (uint8_t)st; }
+			if (lane == 0) { lk_next[f] = make_float2(ox, oy); lk_stat[f] = (uint8_t)st; __threadfence(); }
 		}
 	}
 	__syncthreads();
