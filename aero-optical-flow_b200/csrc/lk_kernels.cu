@@ -877,20 +877,31 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 			if (lane == 0) s_npick[b] = npick;
 		}
 		__syncthreads();
-		// ---- stage 2: concatenate in bin order (x outer, y inner == bin index), thin if too many
-		if (tid == 0) {
-			int n = 0;
-			for (int b = 0; b < LK_BINS; b++)
-				for (int j = 0; j < s_npick[b]; j++) { s_gx[n] = s_px[b][j]; s_gy[n] = s_py[b][j]; n++; }
-			if (n > target) {
-				const int n_remove = n - target, step = target / n_remove + 2;
-				int m = 0;
-				for (int i = 0; i < n; i++)
-					if (i % step) { s_gx[m] = s_gx[i]; s_gy[m] = s_gy[i]; m++; }
-				n = m;
+		// ---- stage 2: concatenate in bin order (x outer, y inner == bin index), thin if too many (every index i with
+		// i % step == 0 is dropped, trackFeatures.cpp:253-264).  Lane b of warp 0 places the picks of bin b: its offset is
+		// a prefix sum of the pick counts, and a kept index i lands at i - (i / step + 1).
+		if (warp == 0) {
+			const int np = lane < LK_BINS ? s_npick[lane] : 0;
+			int incl = np;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+				if (lane >= o) incl += v;
 			}
-			s_ngood = n;
-			s_done = n >= target;
+			const int n = __shfl_sync(0xFFFFFFFFu, incl, 31), off = incl - np;
+			const bool thin = n > target;
+			const int step = thin ? target / (n - target) + 2 : 1;
+			for (int j = 0; j < np; j++) {
+				const int i = off + j;
+				if (thin && i % step == 0) continue;
+				const int m = thin ? i - (i / step + 1) : i;
+				s_gx[m] = s_px[lane][j]; s_gy[m] = s_py[lane][j];
+			}
+			if (lane == 0) {
+				const int kept = thin ? n - (n + step - 1) / step : n;
+				s_ngood = kept;
+				s_done = kept >= target;
+			}
 		}
 		__syncthreads();
 		// ---- stage 3: second chance over every keypoint of the processed bins at dist / 2
