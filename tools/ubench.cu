@@ -56,6 +56,20 @@ template <int OP> __global__ void __launch_bounds__(1024) k(uint32_t *out, uint3
 				asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
 			}
 			if (OP == 12) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+			if (OP == 16) { // packed fp16 min / max (HMNMX2): which pipe, what rate?
+				asm volatile("max.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				asm volatile("min.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+			}
+			if (OP == 17) { // HMNMX2 : VIMNMX3 1:1 -- do they dual-issue?
+				asm volatile("max.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				a[i] = __vimin3_u16x2(a[i], c, b + i);
+			}
+			if (OP == 18) { // HMNMX2 : VIMNMX : VIMNMX3 2:1:1
+				asm volatile("max.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+				asm volatile("min.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+				asm volatile("min.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+				a[i] = __vimax3_u16x2(a[i], b, c + i);
+			}
 		}
 	}
 	uint32_t s = 0;
@@ -80,7 +94,7 @@ template <int OP> void run(const char *name, int sms, int clk_khz, uint32_t *d)
 		float ms; cudaEventElapsedTime(&ms, e0, e1);
 		if (ms < best) best = ms;
 	}
-	double ops = (double)blocks * threads * ITERS * UNROLL * (OP == 11 || OP == 15 ? 2 : OP == 14 ? 3 : 1);
+	double ops = (double)blocks * threads * ITERS * UNROLL * (OP == 11 || OP == 15 || OP == 16 || OP == 17 ? 2 : OP == 14 ? 3 : OP == 18 ? 4 : 1);
 	double per_s = ops / (best * 1e-3);
 	printf("{\"op\": \"%s\", \"ms\": %.4f, \"thread_ops_per_s\": %.4e, \"lanes_per_clk_per_sm_at_max_clk\": %.2f}\n", name, best,
 	       per_s, per_s / sms / (clk_khz * 1e3));
@@ -104,6 +118,9 @@ int main()
 	run<9>("dp4a+prmt 1:1", p.multiProcessorCount, clk, d);
 	run<10>("dp4a+imad 1:1", p.multiProcessorCount, clk, d);
 	run<11>("vimnmx.u16x2 (max,min alternating)", p.multiProcessorCount, clk, d);
+	run<16>("hmnmx2 (max,min f16x2)", p.multiProcessorCount, clk, d);
+	run<17>("hmnmx2+vimnmx3 1:1", p.multiProcessorCount, clk, d);
+	run<18>("hmnmx2+vimnmx+vimnmx3 2:1:1", p.multiProcessorCount, clk, d);
 	run<12>("imad.hi", p.multiProcessorCount, clk, d);
 	run<13>("vimnmx3.u16x2", p.multiProcessorCount, clk, d);
 	run<14>("vimnmx+vimnmx3 2:1", p.multiProcessorCount, clk, d);
