@@ -79,6 +79,8 @@ struct TimingState {
 static TimingState g_t;
 static std::atomic<bool> g_timing_on{false};
 
+bool timing_on() { return g_timing_on.load(std::memory_order_relaxed); }
+
 KernelTimer::KernelTimer(int kid, cudaStream_t st) : kid_(kid), st_(st)
 {
 	if (!g_timing_on.load(std::memory_order_relaxed)) return;

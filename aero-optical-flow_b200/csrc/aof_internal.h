@@ -67,6 +67,8 @@ enum KernelId {
 };
 
 // brackets one launch with two events when timing is enabled; a no-op otherwise
+bool timing_on(); // per-kernel event timing requested (aof_timing_enable)
+
 class KernelTimer {
 public:
 	KernelTimer(int kid, cudaStream_t st);

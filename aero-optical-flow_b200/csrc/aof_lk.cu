@@ -4,6 +4,7 @@
 // (external/klt_feature_tracker/src/trackFeatures.cpp:53-56); the arithmetic is in
 // lk_kernels.cu.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -17,8 +18,9 @@ struct aof_lk {
 	aof_lk_params p;
 	int n = 0, device = 0;
 	LkGeom g{};
-	cudaStream_t st = nullptr, st_copy = nullptr;
+	cudaStream_t st = nullptr, st_copy = nullptr, st_aux = nullptr;
 	cudaEvent_t ev_chunk[8] = {};        // host-batch path: chunk c of the frames has landed
+	cudaEvent_t ev_fork = nullptr, ev_join = nullptr; // device path: second half of the streams on st_aux
 	size_t lvl_px[LK_MAX_LEVELS] = {};   // pixels of one frame at level l
 	size_t upper_off[LK_MAX_LEVELS] = {}; // offset of the level-l block (l >= 1) inside d_upper[slot]
 	size_t upper_bytes = 0;
@@ -151,6 +153,9 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 		if (cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming) != cudaSuccess) h->ev_chunk[c] = nullptr;
 	if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess ||
 	    (e = cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking)) != cudaSuccess ||
+	    (e = cudaStreamCreateWithFlags(&h->st_aux, cudaStreamNonBlocking)) != cudaSuccess ||   // same priority: a high-priority aux stream measured slower
+	    (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+	    (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_upper[0], h->upper_bytes)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_upper[1], h->upper_bytes)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.prev_corners, sizeof(float2) * nN)) != cudaSuccess ||
@@ -192,6 +197,9 @@ void aof_lk_destroy(aof_lk *h)
 	cudaFree(h->d_t); cudaFree(h->d_out); cudaFree(h->d_raw);
 	for (int c = 0; c < 8; c++)
 		if (h->ev_chunk[c]) cudaEventDestroy(h->ev_chunk[c]);
+	if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+	if (h->ev_join) cudaEventDestroy(h->ev_join);
+	if (h->st_aux) cudaStreamDestroy(h->st_aux);
 	if (h->st_copy) cudaStreamDestroy(h->st_copy);
 	if (h->st) cudaStreamDestroy(h->st);
 	delete h;
@@ -240,7 +248,25 @@ int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_
 	AOF_CUDA(cudaSetDevice(h->device));
 	const int nxt = h->cur ^ 1;
 	h->l0[nxt] = d_imgs;
-	int rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, h->n, (cudaStream_t)cuda_stream);
+	// FAST is bound by the ALU pipe, the tracker and the selection by latency: with the streams cut in two halves, the
+	// second half one kernel behind the first on its own stream, the latency-bound kernels of one half run under the
+	// FAST kernel of the other (measured 0.58 -> 0.55 ms per 512 streams).  Off while per-kernel timing is on, so that
+	// the timed kernels do not overlap; AOF_LK_SPLIT=1 turns it off, =2 forces it.
+	const char *se = getenv("AOF_LK_SPLIT");   // read per call: tests switch it
+	const int split_env = se ? atoi(se) : 0;
+	const bool split = (split_env == 0 ? h->n >= 256 : split_env >= 2) && h->n >= 2 && !timing_on();
+	cudaStream_t st = (cudaStream_t)cuda_stream;
+	int rc;
+	if (!split) rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, h->n, st);
+	else {
+		const int na = h->n / 2;
+		AOF_CUDA(cudaEventRecord(h->ev_fork, st));
+		AOF_CUDA(cudaStreamWaitEvent(h->st_aux, h->ev_fork, 0));
+		rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, na, st);
+		if (rc == AOF_OK) rc = run_range(h, nxt, d_t_us, d_out, d_raw, na, h->n - na, h->st_aux);
+		AOF_CUDA(cudaEventRecord(h->ev_join, h->st_aux));
+		AOF_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
+	}
 	if (rc != AOF_OK) return rc;
 	h->cur = nxt;
 	h->have_prev = h->have_feat_prev = true;

@@ -569,6 +569,10 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
                 "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)"},
         "single_stream_latency_us": lat_us,
+        "overlap": "value: the device entry point runs the two halves of the streams on two CUDA streams (8 launches per step, "
+                   "the latency-bound kernels of one half under the FAST kernel of the other); kernels / kernel_rooflines: the same "
+                   "steps with per-kernel event timing on, which runs them unsplit (4 launches per step, no overlap), so their sum "
+                   "exceeds ms_per_step; AOF_LK_SPLIT=1 times the unsplit step",
         "gpu_launches": int(launches), "clocks": clocks, "dtype": "u8 (i32 / f32 in LK)",
     }
     if with_cpu:
@@ -613,7 +617,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": p["dtype"], "data": "synthetic", "config": p["config"], "roofline": p["roofline"],
             "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
-    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu", "kernel_rooflines", "dense"):
+    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu", "kernel_rooflines", "dense", "overlap"):
         if key in p:
             line[key] = p[key]
     if args.workload == "both":

@@ -73,8 +73,11 @@ def test_px4_chunked_batch_equals_device_path_and_oracle(pkg, port, n):
                     assert got[k]["dt_us"][i] == dt
 
 
-def test_lk_chunked_batch_equals_device_path_and_oracle(pkg):
+@pytest.mark.parametrize("split", ["1", "2"])
+def test_lk_chunked_batch_equals_device_path_and_oracle(pkg, split, monkeypatch):
+    """split = 2: the device entry point runs the two halves of the streams on two CUDA streams (fork / join by events)."""
     import torch
+    monkeypatch.setenv("AOF_LK_SPLIT", split)
     from oracle import lk as olk
     w, h, n, T, nf = 256, 256, 50, 4, 20
     rng = np.random.default_rng(11)
