@@ -367,6 +367,12 @@ __device__ int lk_track_point(const LkGeom &g, const LkPyr &prev, const LkPyr &n
 			pdx = ddx; pdy = ddy;
 		}
 	}
+	// calcOpticalFlowPyrLK re-tests the window origin of the final position at level 0 when the caller asks for
+	// the error vector, as trackFeatures.cpp:94,98 does: a last update that left the range clears the status
+	if (status) {
+		const int fx = (int)floorf(nx - half), fy = (int)floorf(ny - half);
+		if (fx < -LK_WIN || fx >= g.w[0] || fy < -LK_WIN || fy >= g.h[0]) status = 0;
+	}
 	out_x = nx; out_y = ny;
 	return status;
 }

@@ -49,14 +49,40 @@ def lib():
     L.olk_set_camera_matrix.restype = None
     L.olk_set_camera_distortion.argtypes = [C.c_void_p] + [C.c_float] * 5
     L.olk_set_camera_distortion.restype = None
+    L.olk_set_params.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_float]
+    L.olk_set_params.restype = None
     L.olk_undistort.argtypes = [f32p, f32p, f32p]
     L.olk_undistort.restype = None
     L.olk_min_eig.argtypes = [u8p, C.c_int, C.c_int, f32p]
     L.olk_min_eig.restype = None
     L.olk_gftt.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, f32p]
     L.olk_gftt.restype = C.c_int
+    L.olk_set_sort_hook.argtypes = [C.c_void_p]
+    L.olk_set_sort_hook.restype = None
     _L = L
     return L
+
+
+def tie_sensitive_sorts(reset=True):
+    """Sort calls since the last reset whose outcome depends on an unstable sort's tie order (> 16 elements with a tie)."""
+    L = lib()
+    L.olk_tie_sensitive_sorts.restype = C.c_long
+    return L.olk_tie_sensitive_sorts(1 if reset else 0)
+
+
+_STD = None
+
+
+def use_std_sort(on):
+    """Test hook: order response ties as libstdc++'s std::sort with the reference's comparator does
+    (oracle/stdsort_shim.cpp) instead of the deterministic (response desc, raster asc) order.  Process-wide."""
+    global _STD
+    if on and _STD is None:
+        so = os.path.join(HERE, "liboracle_stdsort.so")
+        if not os.path.exists(so):
+            subprocess.run(["make", "-s", "-C", HERE, so], check=True, stdout=subprocess.DEVNULL)
+        _STD = C.CDLL(so)
+    lib().olk_set_sort_hook(C.cast(_STD.olk_std_sort, C.c_void_p) if on else None)
 
 
 def _p(a, t):
@@ -142,6 +168,9 @@ class Tracker:
 
     def set_camera_distortion(self, k1, k2, k3, p1=0.0, p2=0.0):
         lib().olk_set_camera_distortion(self.h_, k1, k2, k3, p1, p2)
+
+    def set_params(self, fx, fy, rate, conf):
+        lib().olk_set_params(self.h_, fx, fy, rate, conf)
 
     def calc_flow(self, img, t_us):
         img = np.ascontiguousarray(img, np.uint8)

@@ -224,6 +224,13 @@ void olk_track(const u8 *const *pyr_prev, const u8 *const *pyr_next, const int *
 				}
 				pdx = ddx; pdy = ddy;
 			}
+			/* OpenCV re-tests the window origin of the FINAL position at level 0 when the caller asks for the
+			 * error vector (the reference does: trackFeatures.cpp:94,98; cv2 always does) and clears the status
+			 * if the last update pushed it out of range; the error itself is never read by the reference. */
+			if (level == 0 && status[p]) {
+				const int fx_ = (int)floorf(pts_next[2 * p] - half), fy_ = (int)floorf(pts_next[2 * p + 1] - half);
+				if (fx_ < -win || fx_ >= w || fy_ < -win || fy_ >= h) status[p] = 0;
+			}
 		}
 	}
 }
@@ -359,6 +366,13 @@ void olk_free(olk_tracker *t)
 	free(t);
 }
 
+/* Test hook: replaces the deterministic sort below by a caller-supplied one.  tests/test_ref_lk.py installs
+ * libstdc++'s own std::sort with the reference's response-only comparator (oracle/stdsort_shim.cpp), which makes
+ * this restatement reproduce the reference objects bit for bit on inputs full of response ties as well. */
+typedef void (*olk_sort_fn)(olk_kp *kps, size_t n, int W);
+static olk_sort_fn sort_hook;
+void olk_set_sort_hook(olk_sort_fn fn) { sort_hook = fn; }
+
 /* descending response, ties by raster index ascending (documented divergence from std::sort) */
 static int kp_cmp(const void *a, const void *b, void *wp)
 {
@@ -367,6 +381,33 @@ static int kp_cmp(const void *a, const void *b, void *wp)
 	if (p->resp != q->resp) return q->resp - p->resp;
 	const long ip = (long)p->y * W + p->x, iq = (long)q->y * W + q->x;
 	return ip < iq ? -1 : ip > iq;
+}
+
+/* Number of sort calls since the last reset whose result depends on how ties are ordered by an UNSTABLE sort:
+ * more than 16 elements (libstdc++ sorts <= 16 by a stable insertion sort) and two DIFFERENT keypoints of equal
+ * response among them. */
+static long tie_sensitive_sorts;
+long olk_tie_sensitive_sorts(int reset)
+{
+	const long v = tie_sensitive_sorts;
+	if (reset) tie_sensitive_sorts = 0;
+	return v;
+}
+
+static void sort_kps(olk_kp *kps, size_t n, int W)
+{
+	if (n > 16) {
+		int first[256]; /* index + 1 of the first keypoint with this response; the same keypoint listed twice
+				   (trackFeatures.cpp:212,245-247 can do that) is interchangeable with itself */
+		memset(first, 0, sizeof first);
+		for (size_t i = 0; i < n; i++) {
+			const int r = kps[i].resp & 255;
+			if (first[r] && (kps[first[r] - 1].x != kps[i].x || kps[first[r] - 1].y != kps[i].y)) { tie_sensitive_sorts++; break; }
+			if (!first[r]) first[r] = (int)i + 1;
+		}
+	}
+	if (sort_hook) sort_hook(kps, n, W);
+	else qsort_r(kps, n, sizeof(olk_kp), kp_cmp, (void *)&W);
 }
 
 static int too_close_existing(const olk_tracker *t, int x, int y, unsigned dist)
@@ -419,7 +460,7 @@ static void init_more_points(olk_tracker *t, const u8 *img, int *status, float *
 			for (int yy = 0; yy < bh; yy++)
 				for (int xx = 0; xx < bw; xx++)
 					if (score[yy * bw + xx]) { kps[nk].x = xx + c0; kps[nk].y = yy + r0; kps[nk].resp = score[yy * bw + xx]; nk++; }
-			qsort_r(kps, nk, sizeof(olk_kp), kp_cmp, (void *)&W);
+			sort_kps(kps, nk, W);
 			olk_kp *bin_good = good + n_good;
 			int n_bin = 0;
 			size_t idx = 0;
@@ -444,7 +485,7 @@ static void init_more_points(olk_tracker *t, const u8 *img, int *status, float *
 		n_good = m;
 	}
 	if (n_good < target) {
-		qsort_r(unused, n_unused, sizeof(olk_kp), kp_cmp, (void *)&W);
+		sort_kps(unused, n_unused, W);
 		dist /= 2;
 		for (size_t i = 0; i < n_unused; i++) {
 			const int nx = unused[i].x, ny = unused[i].y;
@@ -533,15 +574,22 @@ void olk_set_camera_matrix(olk_tracker *t, float fx, float fy, float cx, float c
 	t->cam[0] = fx; t->cam[1] = fy; t->cam[2] = cx; t->cam[3] = cy; t->have_cam = 1;
 }
 
+/* setFocalLengthX/Y, setOutputRate (optical_flow.hpp:76-78), setConfMultiplier (flow_opencv.hpp:73): plain
+ * assignments, all tracker / limiter state is kept */
+void olk_set_params(olk_tracker *t, float fx, float fy, int rate, float conf)
+{
+	t->focal_x = fx; t->focal_y = fy; t->output_rate = rate; t->conf = conf;
+}
+
 /* argument order of OpticalFlowOpenCV::setCameraDistortion(k1, k2, k3, p1, p2) */
 void olk_set_camera_distortion(olk_tracker *t, float k1, float k2, float k3, float p1, float p2)
 {
 	t->dc[0] = k1; t->dc[1] = k2; t->dc[2] = p1; t->dc[3] = p2; t->dc[4] = k3; t->have_dist = 1;
 }
 
-/* cv::undistortPoints(src, dst, K, D) (no R, no P; 5 fixed-point iterations, in double) followed by the
- * re-projection of flow_opencv.cpp:113-118 (in float) */
-void olk_undistort(const float cam[4], const float dc[5], float *pt)
+/* cv::undistortPoints(src, dst, K, D) (no R, no P; 5 fixed-point iterations, in double): normalised coordinates,
+ * rounded to f32 as cv::Point2f stores them */
+void olk_undistort_norm(const float cam[4], const float dc[5], const float *pt, float *out)
 {
 	const double fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3];
 	const double k1 = dc[0], k2 = dc[1], p1 = dc[2], p2 = dc[3], k3 = dc[4];
@@ -557,9 +605,16 @@ void olk_undistort(const float cam[4], const float dc[5], float *pt)
 		const double dy = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y + 0 * r2 + 0 * r2 * r2;
 		x = (x0 - dx) * icdist; y = (y0 - dy) * icdist;
 	}
-	const float xf = (float)x, yf = (float)y;
-	pt[0] = xf * cam[0] + cam[2];
-	pt[1] = yf * cam[1] + cam[3];
+	out[0] = (float)x; out[1] = (float)y;
+}
+
+/* olk_undistort_norm followed by the re-projection of flow_opencv.cpp:113-118 (in float) */
+void olk_undistort(const float cam[4], const float dc[5], float *pt)
+{
+	float n[2];
+	olk_undistort_norm(cam, dc, pt, n);
+	pt[0] = n[0] * cam[0] + cam[2];
+	pt[1] = n[1] * cam[1] + cam[3];
 }
 
 /* flow_opencv.cpp:89-210 */

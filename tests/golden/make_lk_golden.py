@@ -1,6 +1,7 @@
 """Generates tests/golden/lk_golden.json from cv2 4.13 (the oracle of record for the OpenCV
 arithmetic) and from tests/cv2_restatement.py (the reference's
-trackFeatures + flow_opencv logic driven through cv2).  Run in the authoring container:
+trackFeatures + flow_opencv logic driven through cv2), and -- "seq_ref" -- from the reference's own LK objects
+(oracle/_ref/libaof_ref_lk.so) with cv2 behind them.  Run in the authoring container:
     python tests/golden/make_lk_golden.py
 The fixture pins oracle/lk_oracle.c on machines without cv2."""
 import hashlib
@@ -68,5 +69,24 @@ for (w, h, dx, dy, seed, rate, nf, T) in [(640, 480, -3, 2, 0, -1, 20, 10), (640
         rows.append({"q": q, "dt": dt, "fx": fx, "fy": fy, "inliers": B.inliers, "px": list(B.px),
                      "update": list(B.update), "fast_bins": B.fast_bins})
     out["seq"].append({"w": w, "h": h, "dx": dx, "dy": dy, "seed": seed, "rate": rate, "nf": nf, "rows": rows})
+# calcFlow sequences from the REFERENCE'S OWN OBJECTS (oracle/_ref/libaof_ref_lk.so: trackFeatures.cpp, flow_opencv.cpp,
+# optical_flow.cpp compiled unmodified) with cv2 executing behind their three OpenCV calls.  These carry the
+# reference's real std::sort tie order; tests/test_ref_lk.py replays them on the oracle with libstdc++'s sort installed.
+from oracle import ref_lk  # noqa: E402
+
+out["seq_ref"] = []
+for (w, h, dx, dy, seed, rate, nf, T) in [(640, 480, -3, 2, 0, -1, 20, 10), (640, 480, -3, 2, 1, 15, 20, 12),
+                                           (128, 128, 2, -1, 2, -1, 20, 10), (128, 128, 1, 1, 3, 15, 20, 14),
+                                           (64, 64, 1, 0, 4, -1, 20, 8), (320, 240, -5, 4, 5, -1, 33, 8)]:
+    fr = pkg.synth.lk_sequence(T, w, h, dx, dy, seed=seed)
+    R = ref_lk.RefTracker(FX, FY, rate, w, h, nf, backend="cv2")
+    rows = []
+    for k in range(T):
+        q, dt, fx, fy = R.calc_flow(fr[k], 1000 + 13333 * k)
+        st = R.state()
+        rows.append({"q": q, "dt": dt, "fx": fx, "fy": fy, "update": st["update_vec"].tolist(),
+                     "feat": st["feat_cur"].astype(np.float64).tolist()})
+    R.close()
+    out["seq_ref"].append({"w": w, "h": h, "dx": dx, "dy": dy, "seed": seed, "rate": rate, "nf": nf, "rows": rows})
 json.dump(out, open(os.path.join(HERE, "lk_golden.json"), "w"))
 print("wrote lk_golden.json", os.path.getsize(os.path.join(HERE, "lk_golden.json")))

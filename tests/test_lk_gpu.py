@@ -115,6 +115,20 @@ def test_track_points_batch_borders(pkg):
     f.close()
 
 
+def test_track_points_final_position_retest(pkg):
+    """the level-0 re-test of the final window origin (cv2 known answer, tests/test_oracle_lk.py) + the band around it"""
+    fr = pkg.synth.lk_sequence(2, 160, 120, 3, 0, seed=75)
+    rng = np.random.default_rng(5)
+    pts = np.stack([161 + rng.uniform(-0.3, 0.3, 2000), rng.uniform(10, 110, 2000)], 1).astype(np.float32)
+    pts[0] = [160.72454833984375, 53.756690979003906]
+    f = pkg.LkFlow(FX, FY, -1, 160, 120)
+    out, st = f.track_points(fr[0][None], fr[1][None], pts[None])
+    o_out, o_st = olk.lk(fr[0], fr[1], pts)
+    assert st[0][0] == 0 and np.array_equal(st[0], o_st)
+    assert np.array_equal(out[0][o_st == 1], o_out[o_st == 1])
+    f.close()
+
+
 def check_state(gs, i, os_):
     uv = gs["update_vec"][i]
     assert list(uv) == list(os_["update_vec"])

@@ -150,3 +150,37 @@ def test_undistort_known_answers():
     assert np.abs(lk.undistort(cam, (0, 0, 0, 0, 0), pts) - pts).max() < 1e-4
     got = lk.undistort(cam, dc, pts)
     assert np.array_equal(got[0], [64, 64]) and (np.abs(got[1:] - pts[1:]).max(1) > 0.01).all()
+
+
+def test_lk_final_position_retest_known_answer(pkg):
+    """calcOpticalFlowPyrLK re-tests the window origin of the FINAL position at level 0 when the error vector is
+    requested (trackFeatures.cpp:94,98 does; cv2 always does): a point whose last update crosses the range ends with
+    status 0.  Found by searching the band x = cols + 4 - dx; cv2 4.13 answers 0 for it, a tracker without the re-test 1."""
+    fr = pkg.synth.lk_sequence(2, 160, 120, 3, 0, seed=75)
+    pts = np.array([[160.72454833984375, 53.756690979003906], [80.0, 60.0]], np.float32)
+    out, st = lk.lk(fr[0], fr[1], pts)
+    assert list(st) == [0, 1]
+    ox = np.floor(out[0, 0] - 4)
+    assert ox < -9 or ox >= 160                     # it was the final update that left the range
+    if cv2 is not None:
+        c, cs, _ = cv2.calcOpticalFlowPyrLK(fr[0], fr[1], pts.reshape(-1, 1, 2), None, winSize=(9, 9), maxLevel=3)
+        assert list(cs.reshape(-1)) == [0, 1] and np.abs(c.reshape(-1, 2) - out).max() <= PX_TOL
+
+
+@pytest.mark.skipif(cv2 is None, reason="cv2 not importable")
+def test_lk_status_at_the_range_boundary_vs_cv2_live(pkg):
+    rng = np.random.default_rng(3)
+    for seed, (dx, dy) in enumerate([(3, 0), (-3, 0), (0, 3), (0, -3)]):
+        fr = pkg.synth.lk_sequence(2, 160, 120, dx, dy, seed=75 + seed)
+        n = 1500
+        band = rng.uniform(-0.3, 0.3, n)
+        if dx:
+            x0 = 160 + 4 - dx if dx > 0 else -9 + 4 - dx
+            pts = np.stack([x0 + band, rng.uniform(10, 110, n)], 1)
+        else:
+            y0 = 120 + 4 - dy if dy > 0 else -9 + 4 - dy
+            pts = np.stack([rng.uniform(10, 150, n), y0 + band], 1)
+        pts = pts.astype(np.float32)
+        o, s = lk.lk(fr[0], fr[1], pts)
+        c, cs, _ = cv2.calcOpticalFlowPyrLK(fr[0], fr[1], pts.reshape(-1, 1, 2), None, winSize=(9, 9), maxLevel=3)
+        assert np.array_equal(s, cs.reshape(-1))
