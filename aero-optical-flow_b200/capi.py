@@ -94,6 +94,8 @@ def lib():
     L.aof_lk_calc_flow_batch.argtypes = [vp, u8p, u32p, vp, vp]
     L.aof_lk_calc_flow_device.argtypes = [vp, u8p, u32p, vp, vp, vp]
     L.aof_lk_get_state.argtypes = [vp, vp, vp, vp, vp]
+    L.aof_px4_set_params.argtypes = [vp, C.c_float, C.c_float, C.c_int]
+    L.aof_lk_set_params.argtypes = [vp, C.c_float, C.c_float, C.c_int, C.c_float]
     L.aof_lk_set_camera_matrix.argtypes = [vp] + [C.c_float] * 4
     L.aof_lk_set_camera_distortion.argtypes = [vp] + [C.c_float] * 5
     L.aof_lk_pyramid.argtypes = [vp, u8p, C.c_int, vp, vp, vp]
@@ -180,6 +182,10 @@ class Px4Flow:
         check(lib().aof_px4_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), _ptr(out)), "aof_px4_calc_flow_batch")
         return out
 
+    def set_params(self, focal_x, focal_y, output_rate):
+        """setFocalLengthX/Y, setOutputRate on the live handle: previous frames and limiter state are kept."""
+        check(lib().aof_px4_set_params(self.handle, focal_x, focal_y, output_rate), "aof_px4_set_params")
+
     def calc_flow_device(self, d_imgs, d_t_us, d_out, d_raw=0, d_blocks=0, stream=0):
         """Raw device pointers (ints); asynchronous on `stream`."""
         check(lib().aof_px4_calc_flow_device(self.handle, d_imgs, d_t_us, d_out, d_raw or None, d_blocks or None,
@@ -237,6 +243,10 @@ class LkFlow:
         check(lib().aof_lk_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), _ptr(out),
                                            _ptr(raw) if want_raw else None), "aof_lk_calc_flow_batch")
         return (out, raw) if want_raw else out
+
+    def set_params(self, focal_x, focal_y, output_rate, conf_multi):
+        """setFocalLengthX/Y, setOutputRate, setConfMultiplier on the live handle: all state is kept."""
+        check(lib().aof_lk_set_params(self.handle, focal_x, focal_y, output_rate, conf_multi), "aof_lk_set_params")
 
     def set_camera_matrix(self, fx, fy, cx, cy):
         check(lib().aof_lk_set_camera_matrix(self.handle, fx, fy, cx, cy), "aof_lk_set_camera_matrix")

@@ -25,6 +25,7 @@ private:
 		const char *dev = std::getenv("AOF_DEVICE");
 		const int rc = aof_px4_create(&p, 1, dev ? std::atoi(dev) : 0, &handle);
 		aof_dirty = false;
+		aof_retune = false;
 		return rc;
 	}
 
@@ -49,6 +50,10 @@ public:
 		if (aof_dirty || !handle) {
 			const int rc = build();
 			if (rc != AOF_OK) return aof_fail("aof_px4_create", rc);
+		}
+		if (aof_retune) {
+			aof_px4_set_params(handle, focal_length_x, focal_length_y, output_rate);
+			aof_retune = false;
 		}
 		const int q = aof_px4_calc_flow(handle, img_current, img_time_us, &dt_us, &flow_x, &flow_y);
 		return q <= AOF_ERR_BASE ? aof_fail("aof_px4_calc_flow", q) : q;

@@ -25,7 +25,13 @@ protected:
 	float sum_flow_y = 0.f;
 	int sum_flow_quality = 0;
 	int valid_frame_count = 0;
-	bool aof_dirty = true; // a setter ran since the device object was built
+	// The reference's setters only assign (include/optical_flow.hpp:74-78) and every object keeps its state.
+	// Here a change of GEOMETRY (width, height, feature count) rebuilds the device object -- the reference
+	// would index its old buffers with the new sizes -- while focal length, output rate and the confidence
+	// multiplier are forwarded to the live handle (aof_*_set_params): tracker, limiter sums and the time of
+	// the last publish survive, as they do in the reference.
+	bool aof_dirty = true;   // geometry changed since the device object was built
+	bool aof_retune = false; // focal length / rate / confidence changed since they were last forwarded
 
 	// no exceptions cross this API (the reference has none): failures are reported on stderr
 	// and calcFlow answers -1 ("do not publish", src/optical_flow.cpp:92)
@@ -40,9 +46,9 @@ public:
 
 	inline void setImageWidth(int img_width) { image_width = img_width; aof_dirty = true; }
 	inline void setImageHeight(int img_height) { image_height = img_height; aof_dirty = true; }
-	inline void setFocalLengthX(float f_lengh) { focal_length_x = f_lengh; aof_dirty = true; }
-	inline void setFocalLengthY(float f_lengh) { focal_length_y = f_lengh; aof_dirty = true; }
-	inline void setOutputRate(int out_rate) { output_rate = out_rate; aof_dirty = true; }
+	inline void setFocalLengthX(float f_lengh) { focal_length_x = f_lengh; aof_retune = true; }
+	inline void setFocalLengthY(float f_lengh) { focal_length_y = f_lengh; aof_retune = true; }
+	inline void setOutputRate(int out_rate) { output_rate = out_rate; aof_retune = true; }
 
 	inline int getImageWidth() { return image_width; }
 	inline int getImageHeight() { return image_height; }

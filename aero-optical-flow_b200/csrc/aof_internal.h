@@ -86,6 +86,10 @@ cudaError_t sad_flow_launch(int search, const uint8_t *prev, const uint8_t *cur,
 bool sad_flow2_supported(const SadGeom &g);
 cudaError_t sad_flow2_launch(int search, const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n,
 			     aof_px4_raw *raw, aof_px4_block *blocks, cudaStream_t st);
+// third version (sad_flow3.cu): 64x64, search 4 only; everything static, paired x-displacements
+bool sad_flow3_supported(int search, const SadGeom &g);
+cudaError_t sad_flow3_launch(const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n, aof_px4_raw *raw,
+			     aof_px4_block *blocks, cudaStream_t st);
 cudaError_t px4_epilogue_launch(const aof_px4_raw *raw, const uint32_t *t_us, LimiterState *lim, aof_flow_out *out,
 				int n, int output_rate, float fx, float fy, cudaStream_t st);
 

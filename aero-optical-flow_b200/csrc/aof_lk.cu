@@ -341,6 +341,16 @@ int aof_lk_calc_flow(aof_lk *h, const uint8_t *img, uint32_t img_time_us, int *d
 	return o.quality;
 }
 
+/* setFocalLengthX/Y, setOutputRate (include/optical_flow.hpp:76-78), setConfMultiplier (include/flow_opencv.hpp:73) */
+int aof_lk_set_params(aof_lk *h, float focal_length_x, float focal_length_y, int output_rate, float confidence_multiplier)
+{
+	if (!h) { set_error("aof_lk_set_params: null handle"); return AOF_ERR_INVALID; }
+	// passed to the selection / epilogue kernel by value on every call: nothing on the device changes
+	h->p.focal_length_x = focal_length_x; h->p.focal_length_y = focal_length_y; h->p.output_rate = output_rate;
+	h->p.confidence_multiplier = confidence_multiplier;
+	return AOF_OK;
+}
+
 /* OpticalFlowOpenCV::setCameraMatrix (src/flow_opencv.cpp:72-80) */
 int aof_lk_set_camera_matrix(aof_lk *h, float focal_len_x, float focal_len_y, float principal_point_x, float principal_point_y)
 {

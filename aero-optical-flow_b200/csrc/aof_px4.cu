@@ -57,7 +57,9 @@ int aof_px4_create(const aof_px4_params *p, int n_streams, int device, aof_px4 *
 	if (!p || !out || n_streams < 1) { set_error("aof_px4_create: bad argument"); return AOF_ERR_INVALID; }
 	*out = nullptr;
 	const int W = p->image_width, H = p->image_height, S = p->search_size;
-	if (S != 4 && S != 6 && S != 8) { set_error("search_size %d not built (4, 6, 8)", S); return AOF_ERR_UNSUPPORTED; }
+	// any search size the reference's int8_t displacement loop can express (px4flow.cpp:393-396); 4, 6 and 8 have
+	// specialised kernels, the rest run sad_flow_any_kernel
+	if (S < 1 || S > 127) { set_error("search_size %d out of range (1..127)", S); return AOF_ERR_UNSUPPORTED; }
 	// the reference grid uses image_width on both axes (px4flow.cpp:360,380) and 16-bit
 	// pixel offsets (:117,304): its valid domain is H >= W, W*H <= 65535.
 	if (W < 2 * (S + 1) + 8 + 1 || H < W || (long)W * H > 65535 || (W & 3) || ((W * H) & 15)) {
@@ -97,6 +99,14 @@ int aof_px4_create(const aof_px4_params *p, int n_streams, int device, aof_px4 *
 	return AOF_OK;
 }
 
+int aof_px4_set_params(aof_px4 *h, float focal_length_x, float focal_length_y, int output_rate)
+{
+	if (!h) { set_error("aof_px4_set_params: null handle"); return AOF_ERR_INVALID; }
+	// passed to the epilogue kernel by value on every call: nothing on the device changes
+	h->p.focal_length_x = focal_length_x; h->p.focal_length_y = focal_length_y; h->p.output_rate = output_rate;
+	return AOF_OK;
+}
+
 void aof_px4_destroy(aof_px4 *h)
 {
 	if (!h) return;
@@ -131,6 +141,10 @@ int aof_px4_calc_flow_device(aof_px4 *h, const uint8_t *d_imgs, const uint32_t *
 			     aof_px4_raw *d_raw, aof_px4_block *d_blocks, void *cuda_stream)
 {
 	if (!h || !d_imgs || !d_t_us || !d_out) { set_error("calc_flow_device: null argument"); return AOF_ERR_INVALID; }
+	if ((uintptr_t)d_imgs & 15) { // the kernels stage frames with cp.async.bulk: a misaligned source faults the context
+		set_error("calc_flow_device: d_imgs must be 16-byte aligned");
+		return AOF_ERR_INVALID;
+	}
 	AOF_CUDA(cudaSetDevice(h->device));
 	cudaStream_t st = (cudaStream_t)cuda_stream;
 	if (!h->primed) { // first frame: remember it, report quality 0 (flow_px4.cpp:73-78)
@@ -239,6 +253,10 @@ int aof_px4_compute_flow_pairs_device(aof_px4 *h, const uint8_t *d_prev, const u
 				      aof_px4_raw *d_raw, aof_px4_block *d_blocks, void *cuda_stream)
 {
 	if (!h || !d_prev || !d_cur || !d_raw || n < 0) { set_error("compute_flow_pairs_device: bad argument"); return AOF_ERR_INVALID; }
+	if (((uintptr_t)d_prev | (uintptr_t)d_cur) & 15) {
+		set_error("compute_flow_pairs_device: d_prev and d_cur must be 16-byte aligned");
+		return AOF_ERR_INVALID;
+	}
 	AOF_CUDA(cudaSetDevice(h->device));
 	AOF_CUDA(sad_flow_launch(h->p.search_size, d_prev, d_cur, h->g, n, d_raw, d_blocks, (cudaStream_t)cuda_stream));
 	return AOF_OK;

@@ -52,7 +52,7 @@ typedef struct aof_px4_params {
 	float focal_length_x, focal_length_y; /* px */
 	int output_rate;                      /* Hz; <= 0: publish every frame */
 	int image_width, image_height;
-	int search_size;                      /* +-px; 4, 6 or 8 */
+	int search_size;                      /* +-px; 1..127 (4, 6, 8 have specialised kernels) */
 	int flow_feature_threshold;           /* texture gate (30) */
 	int flow_value_threshold;             /* SAD acceptance (3000) */
 } aof_px4_params;
@@ -111,7 +111,11 @@ int aof_px4_calc_flow_batch(aof_px4 *h, const uint8_t *imgs, const uint32_t *t_u
  * handle's device; launched on `cuda_stream` (a cudaStream_t, NULL = default
  * stream) without synchronising.  d_imgs must stay valid until the NEXT call
  * returns (it becomes the previous frame; no copy is made).  d_raw / d_blocks
- * may be NULL. */
+ * may be NULL.  d_imgs must be 16-byte aligned (the frames are staged with bulk
+ * copies of the TMA engine, which need 16-byte aligned sources; width * height is
+ * a multiple of 16 by construction): a misaligned pointer is AOF_ERR_INVALID.
+ * One CUDA stream per handle: successive calls must be issued on the same stream
+ * (or be ordered by the caller), because they read and write handle-owned state. */
 int aof_px4_calc_flow_device(aof_px4 *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
 			     aof_px4_raw *d_raw, aof_px4_block *d_blocks, void *cuda_stream);
 
@@ -119,12 +123,17 @@ int aof_px4_calc_flow_device(aof_px4 *h, const uint8_t *d_imgs, const uint32_t *
  * HOST memory; raw[n]; blocks may be NULL or n*AOF_PX4_MAX_BLOCKS entries. */
 int aof_px4_compute_flow_pairs(aof_px4 *h, const uint8_t *prev, const uint8_t *cur, int n, aof_px4_raw *raw,
 			       aof_px4_block *blocks);
-/* same with DEVICE pointers, asynchronous on cuda_stream */
+/* same with DEVICE pointers (16-byte aligned, see above), asynchronous on cuda_stream */
 int aof_px4_compute_flow_pairs_device(aof_px4 *h, const uint8_t *d_prev, const uint8_t *d_cur, int n,
 				      aof_px4_raw *d_raw, aof_px4_block *d_blocks, void *cuda_stream);
 
 /* forget previous frames and limiter state (as a freshly constructed object) */
 int aof_px4_reset(aof_px4 *h);
+
+/* replaces OpticalFlow::setFocalLengthX / setFocalLengthY / setOutputRate (include/optical_flow.hpp:76-78) on a
+ * live handle: plain assignments, as in the reference -- previous frames, limiter sums and the time of the last
+ * publish are kept; the new values apply from the next calc call, to all streams. */
+int aof_px4_set_params(aof_px4 *h, float focal_length_x, float focal_length_y, int output_rate);
 
 /* ------------------------------------------------------------------- LK path */
 
@@ -169,9 +178,17 @@ int aof_lk_calc_flow_batch(aof_lk *h, const uint8_t *imgs, const uint32_t *t_us,
 
 /* device-resident form, asynchronous on cuda_stream.  d_imgs must stay valid
  * and unchanged until the NEXT call has completed (it is level 0 of the previous
- * pyramid; no copy is made).  d_raw may be NULL. */
+ * pyramid; no copy is made).  d_raw may be NULL.  One CUDA stream per handle:
+ * successive calls (and aof_lk_calc_flow_batch, which uses the handle's own stream)
+ * read and write handle-owned state, so issue them on the same stream or order them. */
 int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
 			    aof_lk_raw *d_raw, void *cuda_stream);
+
+/* replaces setFocalLengthX / setFocalLengthY / setOutputRate (include/optical_flow.hpp:76-78) and
+ * OpticalFlowOpenCV::setConfMultiplier (include/flow_opencv.hpp:73) on a live handle: plain assignments, as in the
+ * reference -- tracker state, feature slots, limiter sums and the time of the last publish are kept. */
+int aof_lk_set_params(aof_lk *h, float focal_length_x, float focal_length_y, int output_rate,
+		      float confidence_multiplier);
 
 /* replace OpticalFlowOpenCV::setCameraMatrix / setCameraDistortion (src/flow_opencv.cpp:72-87; note the
  * reference's argument order k1, k2, k3, p1, p2).  As in the reference, feature positions are undistorted

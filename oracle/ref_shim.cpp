@@ -74,6 +74,15 @@ int ref_px4_calc_flow(void *h, uint8_t *img, uint32_t t_us, int *dt_us, float *f
 	return static_cast<OpticalFlowPX4 *>(h)->calcFlow(img, t_us, *dt_us, *fx, *fy);
 }
 
+// the reference's own setters (include/optical_flow.hpp:76-78): they only assign
+void ref_px4_set_params(void *h, float fx, float fy, int rate)
+{
+	OpticalFlowPX4 *o = static_cast<OpticalFlowPX4 *>(h);
+	o->setFocalLengthX(fx);
+	o->setFocalLengthY(fy);
+	o->setOutputRate(rate);
+}
+
 void ref_px4_free(void *h) { delete static_cast<OpticalFlowPX4 *>(h); }
 
 } // extern "C"

@@ -116,6 +116,11 @@ class _PortPX4:
                                      C.byref(px), C.byref(py), C.byref(rq))
         return q, dt.value, fx.value, fy.value, px.value, py.value, rq.value
 
+    def set_params(self, fx, fy, rate):
+        self.L.orc_px4_set_params.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_int]
+        self.L.orc_px4_set_params.restype = None
+        self.L.orc_px4_set_params(self.h, fx, fy, rate)
+
     def __del__(self):
         if getattr(self, "h", None):
             self.L.orc_px4_free(self.h)
@@ -194,6 +199,11 @@ class _RefPX4:
         dt = C.c_int(-123456); fx = C.c_float(np.nan); fy = C.c_float(np.nan)
         q = self.L.ref_px4_calc_flow(self.h, _p(img, u8p), t_us, C.byref(dt), C.byref(fx), C.byref(fy))
         return q, dt.value, fx.value, fy.value
+
+    def set_params(self, fx, fy, rate):
+        self.L.ref_px4_set_params.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_int]
+        self.L.ref_px4_set_params.restype = None
+        self.L.ref_px4_set_params(self.h, fx, fy, rate)
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -229,6 +229,12 @@ orc_px4 *orc_px4_new(float fx, float fy, int rate, int w, int h, int search, int
 	return s;
 }
 
+/* setFocalLengthX/Y, setOutputRate (include/optical_flow.hpp:76-78): plain assignments, all state is kept */
+void orc_px4_set_params(orc_px4 *s, float fx, float fy, int rate)
+{
+	s->focal_x = fx; s->focal_y = fy; s->lim.output_rate = rate;
+}
+
 void orc_px4_free(orc_px4 *s) { if (s) { free(s->prev); free(s); } }
 
 /* src/flow_px4.cpp:69-98.  Also returns the raw pixel flow / raw quality of this

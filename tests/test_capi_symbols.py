@@ -61,9 +61,10 @@ def test_no_cpu_fallback_without_gpu(pkg):
 
 def test_bad_geometry_rejected(pkg):
     L = pkg.lib()
-    p = pkg.capi.Px4Params(200.0, 200.0, 15, 64, 64, 5, 30, 3000)   # search 5 is not built
     h = C.c_void_p()
-    assert L.aof_px4_create(C.byref(p), 1, 0, C.byref(h)) == -101
+    for s in (0, -3, 128):                                           # outside the reference's int8_t displacement loop
+        p = pkg.capi.Px4Params(200.0, 200.0, 15, 64, 64, s, 30, 3000)
+        assert L.aof_px4_create(C.byref(p), 1, 0, C.byref(h)) == -101
     p = pkg.capi.Px4Params(200.0, 200.0, 15, 16, 16, 4, 30, 3000)   # too small for the grid
     assert L.aof_px4_create(C.byref(p), 1, 0, C.byref(h)) == -101
     assert L.aof_px4_create(None, 1, 0, C.byref(h)) == -100

@@ -98,3 +98,21 @@ def test_port_vs_reference_other_widths(port, ref):
             if w < 2 * (s + 1) + 9:
                 continue
             assert port.compute_flow(a, b, s, 30, 6000) == ref.compute_flow(a, b, s, 30, 6000)
+
+
+def test_px4_setters_keep_state_port_vs_reference(pkg, port, ref):
+    """the reference's setters only assign (include/optical_flow.hpp:76-78): the port's set_params must follow the
+    reference objects through a change of focal length and output rate in mid-sequence"""
+    tex = pkg.synth.lcg_texture()
+    frames = [pkg.synth.crop(tex, 100 - 2 * t, 100 + t) for t in range(14)]
+    a = port.px4(216.6677, 216.2457, 15, 64, 64, 4, 30, 3000)
+    b = ref.px4(216.6677, 216.2457, 15, 64, 64, 4, 30, 3000)
+    retune = {4: (300.0, 310.0, 15), 8: (300.0, 310.0, -1), 11: (216.0, 216.0, 20)}
+    for k, f in enumerate(frames):
+        if k in retune:
+            a.set_params(*retune[k]); b.set_params(*retune[k])
+        ra = a.calc_flow(f, 1000 + 13333 * k)[:4]
+        rb = b.calc_flow(f, 1000 + 13333 * k)
+        assert ra[0] == rb[0] and ra[1] == rb[1], k
+        if k:
+            assert ra[2:] == rb[2:], k

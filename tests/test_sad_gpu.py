@@ -170,3 +170,42 @@ def test_full_size_batch_property(pkg):
     back = f.calc_flow_batch(prev, t + 5000)
     assert np.allclose(back["flow_x"], -out["flow_x"], atol=1e-7) and np.allclose(back["flow_y"], -out["flow_y"], atol=1e-7)
     f.close()
+
+
+@pytest.mark.parametrize("s", [1, 2, 3, 5, 7, 10, 26])
+def test_any_search_size_vs_reference_objects(pkg, port, ref, s):
+    """flow_px4.hpp:62-65 takes any search size: sizes without a specialised kernel run sad_flow_any_kernel and
+    must equal the reference objects (and the port, block by block)."""
+    prev, cur, _ = pkg.synth.sad_pairs(40, max_shift=min(s, 8), seed=300 + s, half_pixel_every=3)
+    f = pkg.Px4Flow(FX, FY, -1, 64, 64, s, 30, 3000, n_streams=1)
+    raw, blocks = f.compute_flow_pairs(prev, cur, want_blocks=True)
+    rx, ry, rq = ref.compute_flow_batch(prev, cur, s, 30, 3000)
+    assert np.array_equal(raw["px_x"], rx) and np.array_equal(raw["px_y"], ry) and np.array_equal(raw["quality"], rq)
+    if s <= 10:
+        assert (rq == 255).sum() >= 30          # the run is not vacuous
+    else:
+        assert (rq == 0).all()                  # 64 - 2 * 27 - 8 = 2 px of grid: one position, never > 10 votes
+    for i in (0, 17, 39):
+        check_blocks(port, prev[i], cur[i], blocks[i], s, 30, 3000)
+    f.close()
+
+
+def test_misaligned_device_pointer_is_rejected(pkg):
+    """the device entry points stage frames with bulk (TMA-engine) copies: a source that is not 16-byte aligned is
+    refused with AOF_ERR_INVALID instead of faulting the context (include/aof.h)"""
+    import torch
+    n = 8
+    buf = torch.zeros(n * 4096 * 2 + 64, dtype=torch.uint8, device="cuda")
+    t = torch.zeros(n, dtype=torch.int32, device="cuda")
+    out = torch.zeros(n * 4, dtype=torch.int32, device="cuda")
+    raw = torch.zeros(n * 4, dtype=torch.int32, device="cuda")
+    f = pkg.Px4Flow(FX, FY, -1, 64, 64, 4, 30, 3000, n_streams=n)
+    L = pkg.lib()
+    assert L.aof_px4_calc_flow_device(f.handle, buf.data_ptr() + 1, t.data_ptr(), out.data_ptr(), 0, 0, 0) == -100
+    assert b"16-byte" in L.aof_last_error()
+    assert L.aof_px4_compute_flow_pairs_device(f.handle, buf.data_ptr() + 4, buf.data_ptr() + n * 4096, n, raw.data_ptr(), 0, 0) == -100
+    assert L.aof_px4_compute_flow_pairs_device(f.handle, buf.data_ptr(), buf.data_ptr() + n * 4096 + 8, n, raw.data_ptr(), 0, 0) == -100
+    # the context is still healthy and an aligned call works
+    assert L.aof_px4_compute_flow_pairs_device(f.handle, buf.data_ptr(), buf.data_ptr() + n * 4096, n, raw.data_ptr(), 0, 0) == 0
+    torch.cuda.synchronize()
+    f.close()

@@ -78,3 +78,45 @@ def test_opencv_class_matches_oracle(pkg, mode, rate):
         oq, odt, ofx, ofy = o.calc_flow(frames[k], 1000 + 13333 * k)
         assert (q, fx, fy) == (oq, ofx, ofy), k
         assert dt == (odt if (oq >= 0 or rate <= 0) else -123456)
+
+
+RETUNE = {4: (300.0, 310.0, 15, 1.645), 8: (300.0, 310.0, -1, 1.0), 11: (216.0, 216.0, 20, 2.5)}
+
+
+@pytest.mark.gpu
+def test_px4_setters_keep_state(pkg, port):
+    """setFocalLength* / setOutputRate between frames: the reference's setters only assign
+    (include/optical_flow.hpp:74-78); previous frame, limiter sums and time_last_pub survive."""
+    build_driver(pkg)
+    tex = pkg.synth.lcg_texture()
+    frames = np.stack([pkg.synth.crop(tex, 100 - 2 * t, 100 + t) for t in range(14)])
+    rows = run_driver("px4retune", frames, 15, 13333)
+    o = port.px4(FX, FY, 15, 64, 64, 4, 30, 3000)
+    rate = 15
+    for k, (q, dt, fx, fy) in enumerate(rows):
+        if k in RETUNE:
+            o.set_params(*RETUNE[k][:3])
+            rate = RETUNE[k][2]
+        oq, odt, ofx, ofy, *_ = o.calc_flow(frames[k], 1000 + 13333 * k)
+        assert q == oq, k
+        if k == 0:
+            continue
+        assert abs(fx - ofx) <= 2e-9 + 1.2e-7 * abs(ofx) and abs(fy - ofy) <= 2e-9 + 1.2e-7 * abs(ofy)
+        assert dt == (odt if (oq >= 0 or rate <= 0) else -123456), k
+
+
+@pytest.mark.gpu
+def test_opencv_setters_keep_state(pkg):
+    from oracle import lk as olk
+    build_driver(pkg)
+    frames = np.stack(pkg.synth.lk_sequence(14, 128, 128, 1, 1, seed=34))
+    rows = run_driver("lkretune", frames, 15, 13333)
+    o = olk.Tracker(FX, FY, 15, 128, 128, 20)
+    rate = 15
+    for k, (q, dt, fx, fy) in enumerate(rows):
+        if k in RETUNE:
+            o.set_params(*RETUNE[k])
+            rate = RETUNE[k][2]
+        oq, odt, ofx, ofy = o.calc_flow(frames[k], 1000 + 13333 * k)
+        assert (q, fx, fy) == (oq, ofx, ofy), k
+        assert dt == (odt if (oq >= 0 or rate <= 0) else -123456)
