@@ -2,6 +2,7 @@
 // staging, launch counting and the optional per-kernel CUDA-event timing (aof_timing_*).
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -24,6 +25,12 @@ void set_error(const char *fmt, ...)
 }
 const char *last_error() { return g_err; }
 
+int env_int(const char *name, int dflt)
+{
+	const char *v = getenv(name);
+	return v && *v ? atoi(v) : dflt;
+}
+
 int select_device(int device)
 {
 	int n = 0;
@@ -35,11 +42,17 @@ int select_device(int device)
 	return AOF_OK;
 }
 
-int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStream_t st)
+bool host_pinned(const void *p)
 {
 	cudaPointerAttributes at{};
-	const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+	const bool pinned = cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeHost;
 	cudaGetLastError();
+	return pinned;
+}
+
+int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStream_t st)
+{
+	const bool pinned = host_pinned(src);
 	if (pinned) {
 		AOF_CUDA(cudaMemcpyAsync(d_dst, src, bytes, cudaMemcpyHostToDevice, st));
 		return AOF_OK;

@@ -11,6 +11,8 @@ const char *last_error();
 int select_device(int device);
 // host -> device copy of `bytes` on `st`: directly if `src` is pinned (cudaHostAlloc / cudaHostRegister),
 // else through the pinned staging buffer `stage` (>= bytes) in chunks so the CPU copy overlaps the DMA
+// true when p is page-locked host memory (cudaHostAlloc / cudaHostRegister): DMA can target it directly
+bool host_pinned(const void *p);
 int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStream_t st);
 } // namespace aof
 

@@ -22,7 +22,14 @@ struct SadGeom {
 	int nb;                // grid positions per axis (<= 5)
 	int lo, step;          // first position, spacing
 	uint32_t feat_thr, val_thr;
+	// A/B and grid-shaping switches, read from the environment ONCE when the handle is created (env_int)
+	int tun_v1;            // AOF_SAD_V1 = 1: the CTA-per-pair kernel
+	int tun_v2;            // AOF_SAD_V2 = 1: never sad_flow3_kernel
+	int tun_ctas;          // AOF_SAD_CTAS: cap on resident CTAs per SM (0 = occupancy)
 };
+
+// integer environment switch, read where a handle is created (never on a launch path)
+int env_int(const char *name, int dflt);
 
 // per-stream OpticalFlow rate limiter (include/optical_flow.hpp:61-64 plus the
 // function-static time_last_pub of src/optical_flow.cpp:55, made per stream)
@@ -113,6 +120,12 @@ struct LkGeom {
 	int dist;         // binWidth / targetFeaturesPerBin
 	int kp_cap;       // keypoint-list capacity per bin
 	int fast_thr;     // 10
+	// A/B and tuning switches, read from the environment ONCE in aof_lk_create (env_int)
+	int tun_pyr_bands; // AOF_PYR_BANDS: forced band count of the streaming pyramid kernel (0 = auto)
+	int tun_pyr_occ;   // AOF_PYR_OCC: CTAs per SM the pyramid kernel is compiled for (16 / 20 / 24)
+	int tun_pyr_v1;    // AOF_PYR_V1 = 1: the generic streaming kernel
+	int tun_fast_v1;   // AOF_FAST_V1 = 1: the tile FAST kernel
+	int tun_track_v1;  // AOF_TRACK_V1 = 1: the CTA-per-stream tracker
 };
 
 // level base pointers of one pyramid slot; level l of stream s is at lvl[l] + s * w[l] * h[l]

@@ -14,13 +14,19 @@
 
 using namespace aof;
 
+constexpr int LK_MAX_PARTS = 8;
+
 struct aof_lk {
 	aof_lk_params p;
 	int n = 0, device = 0;
 	LkGeom g{};
-	cudaStream_t st = nullptr, st_copy = nullptr, st_aux = nullptr;
+	cudaStream_t st = nullptr, st_copy = nullptr;
+	cudaStream_t st_hi = nullptr, st_lo = nullptr; // device path pipeline: latency-bound kernels / FAST (see aof_lk_calc_flow_device)
 	cudaEvent_t ev_chunk[8] = {};        // host-batch path: chunk c of the frames has landed
-	cudaEvent_t ev_fork = nullptr, ev_join = nullptr; // device path: second half of the streams on st_aux
+	cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+	cudaEvent_t ev_trk[LK_MAX_PARTS] = {}, ev_fast[LK_MAX_PARTS] = {};
+	int tun_split = 0;                   // AOF_LK_SPLIT: 1 = never pipeline the parts, 2 = always (read once at create)
+	int tun_parts = 0;                   // AOF_LK_PARTS: parts a batch is cut into (0 = by batch size)
 	size_t lvl_px[LK_MAX_LEVELS] = {};   // pixels of one frame at level l
 	size_t upper_off[LK_MAX_LEVELS] = {}; // offset of the level-l block (l >= 1) inside d_upper[slot]
 	size_t upper_bytes = 0;
@@ -148,12 +154,25 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	}
 	h->upper_bytes = off ? off : 256;
 	const size_t nN = (size_t)n_streams * N;
+	// every environment switch of this path is read here, once (never on a launch path)
+	g.tun_pyr_bands = env_int("AOF_PYR_BANDS", 0); g.tun_pyr_occ = env_int("AOF_PYR_OCC", 0);
+	g.tun_pyr_v1 = env_int("AOF_PYR_V1", 0); g.tun_fast_v1 = env_int("AOF_FAST_V1", 0); g.tun_track_v1 = env_int("AOF_TRACK_V1", 0);
+	h->tun_split = env_int("AOF_LK_SPLIT", 0); h->tun_parts = env_int("AOF_LK_PARTS", 0);
 	cudaError_t e;
+	int prio_lo = 0, prio_hi = 0;
+	// measured (r2c): with the latency-bound kernels on a HIGH-priority stream 4 parts take 0.65 ms per 512 streams
+	// against 0.57 for two equal-priority halves -- the small kernels then run one after the other at their latency
+	// floors while FAST waits.  AOF_LK_PRIO=1 turns the priorities on for A/B runs.
+	if (env_int("AOF_LK_PRIO", 0) == 1) cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi); // (least, greatest)
 	for (int c = 0; c < 8; c++)
 		if (cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming) != cudaSuccess) h->ev_chunk[c] = nullptr;
+	for (int c = 0; c < LK_MAX_PARTS; c++)
+		if (cudaEventCreateWithFlags(&h->ev_trk[c], cudaEventDisableTiming) != cudaSuccess ||
+		    cudaEventCreateWithFlags(&h->ev_fast[c], cudaEventDisableTiming) != cudaSuccess) h->ev_trk[c] = h->ev_fast[c] = nullptr;
 	if ((e = cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking)) != cudaSuccess ||
 	    (e = cudaStreamCreateWithFlags(&h->st_copy, cudaStreamNonBlocking)) != cudaSuccess ||
-	    (e = cudaStreamCreateWithFlags(&h->st_aux, cudaStreamNonBlocking)) != cudaSuccess ||   // same priority: a high-priority aux stream measured slower
+	    (e = cudaStreamCreateWithPriority(&h->st_hi, cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
+	    (e = cudaStreamCreateWithPriority(&h->st_lo, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
 	    (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
 	    (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->d_upper[0], h->upper_bytes)) != cudaSuccess ||
@@ -199,13 +218,19 @@ void aof_lk_destroy(aof_lk *h)
 		if (h->ev_chunk[c]) cudaEventDestroy(h->ev_chunk[c]);
 	if (h->ev_fork) cudaEventDestroy(h->ev_fork);
 	if (h->ev_join) cudaEventDestroy(h->ev_join);
-	if (h->st_aux) cudaStreamDestroy(h->st_aux);
+	for (int c = 0; c < LK_MAX_PARTS; c++) {
+		if (h->ev_trk[c]) cudaEventDestroy(h->ev_trk[c]);
+		if (h->ev_fast[c]) cudaEventDestroy(h->ev_fast[c]);
+	}
+	if (h->st_hi) cudaStreamDestroy(h->st_hi);
+	if (h->st_lo) cudaStreamDestroy(h->st_lo);
 	if (h->st_copy) cudaStreamDestroy(h->st_copy);
 	if (h->st) cudaStreamDestroy(h->st);
 	delete h;
 }
 
 int aof_lk_num_streams(const aof_lk *h) { return h ? h->n : AOF_ERR_INVALID; }
+int aof_lk_num_features(const aof_lk *h) { return h ? h->g.n_feat : AOF_ERR_INVALID; }
 
 int aof_lk_reset(aof_lk *h)
 {
@@ -216,9 +241,8 @@ int aof_lk_reset(aof_lk *h)
 	return reset_state(h);
 }
 
-// one calcFlow pass over streams [first, first + count) of the batch whose level 0 is h->l0[nxt]
-static int run_range(aof_lk *h, int nxt, const uint32_t *d_t_us, aof_flow_out *d_out, aof_lk_raw *d_raw, int first, int count,
-		     cudaStream_t st)
+// the four stages of one calcFlow pass over streams [first, first + count) of the batch whose level 0 is h->l0[nxt]
+static int run_pyr_track(aof_lk *h, int nxt, int first, int count, cudaStream_t st)
 {
 	const size_t f = (size_t)first;
 	const LkPyr next = pyr_of(h, nxt, f);
@@ -234,11 +258,33 @@ static int run_range(aof_lk *h, int nxt, const uint32_t *d_t_us, aof_flow_out *d
 		for (int l = 1; l <= h->g.top; l++)
 			AOF_CUDA(lk_pyr_down_launch(next.lvl[l - 1], const_cast<uint8_t *>(next.lvl[l]), h->g.w[l - 1], h->g.h[l - 1], count, st));
 	AOF_CUDA(lk_track_update_launch(h->g, prev, next, sv, count, h->have_prev ? 1 : 0, st));
-	AOF_CUDA(lk_fast_launch(h->g, next.lvl[0], sv, count, nullptr, st));
-	AOF_CUDA(lk_select_epilogue_launch(h->g, sv, d_t_us + f, d_out + f, d_raw ? d_raw + f : nullptr, count,
+	return AOF_OK;
+}
+
+static int run_fast(aof_lk *h, int nxt, int first, int count, cudaStream_t st)
+{
+	const size_t f = (size_t)first;
+	AOF_CUDA(lk_fast_launch(h->g, pyr_of(h, nxt, f).lvl[0], state_from(h->s, h->g, f), count, nullptr, st));
+	return AOF_OK;
+}
+
+static int run_select(aof_lk *h, const uint32_t *d_t_us, aof_flow_out *d_out, aof_lk_raw *d_raw, int first, int count,
+		      cudaStream_t st)
+{
+	const size_t f = (size_t)first;
+	AOF_CUDA(lk_select_epilogue_launch(h->g, state_from(h->s, h->g, f), d_t_us + f, d_out + f, d_raw ? d_raw + f : nullptr, count,
 					   h->have_feat_prev ? 1 : 0, h->p.output_rate, h->p.confidence_multiplier,
 					   h->p.focal_length_x, h->p.focal_length_y, h->cam, st));
 	return AOF_OK;
+}
+
+static int run_range(aof_lk *h, int nxt, const uint32_t *d_t_us, aof_flow_out *d_out, aof_lk_raw *d_raw, int first, int count,
+		     cudaStream_t st)
+{
+	int rc = run_pyr_track(h, nxt, first, count, st);
+	if (rc == AOF_OK) rc = run_fast(h, nxt, first, count, st);
+	if (rc == AOF_OK) rc = run_select(h, d_t_us, d_out, d_raw, first, count, st);
+	return rc;
 }
 
 int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_t_us, aof_flow_out *d_out,
@@ -248,23 +294,41 @@ int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_
 	AOF_CUDA(cudaSetDevice(h->device));
 	const int nxt = h->cur ^ 1;
 	h->l0[nxt] = d_imgs;
-	// FAST is bound by the ALU pipe, the tracker and the selection by latency: with the streams cut in two halves, the
-	// second half one kernel behind the first on its own stream, the latency-bound kernels of one half run under the
-	// FAST kernel of the other (measured 0.58 -> 0.55 ms per 512 streams).  Off while per-kernel timing is on, so that
-	// the timed kernels do not overlap; AOF_LK_SPLIT=1 turns it off, =2 forces it.
-	const char *se = getenv("AOF_LK_SPLIT");   // read per call: tests switch it
-	const int split_env = se ? atoi(se) : 0;
-	const bool split = (split_env == 0 ? h->n >= 256 : split_env >= 2) && h->n >= 2 && !timing_on();
+	// FAST is bound by the ALU pipe (and is two thirds of the step); the pyramid, the tracker and the selection are
+	// bound by latency.  The batch is cut into parts of whole streams and software-pipelined over two internal
+	// streams: the latency-bound kernels of every part go to a HIGH-priority stream, FAST to a LOW-priority one, with
+	// events for the per-part dependencies (track -> FAST -> select).  While FAST of part p fills the SMs, the
+	// pyramid / tracker of part p + 1 and the selection of part p - 1 take the CTA slots that free up first, so only the
+	// head (pyramid + tracker of the first part) and the tail (selection of the last part) are exposed.
+	// Off while per-kernel timing is on (the timed kernels must not overlap); AOF_LK_SPLIT=1 turns it off, =2 forces it,
+	// AOF_LK_PARTS sets the number of parts (both read once, in aof_lk_create).
+	int parts = h->tun_parts > 0 ? h->tun_parts : 2;
+	if (parts > LK_MAX_PARTS) parts = LK_MAX_PARTS;
+	if (parts > h->n) parts = h->n;
+	const bool pipelined = (h->tun_split == 0 ? h->n >= 256 : h->tun_split >= 2) && parts >= 2 && !timing_on() && h->ev_trk[LK_MAX_PARTS - 1];
 	cudaStream_t st = (cudaStream_t)cuda_stream;
-	int rc;
-	if (!split) rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, h->n, st);
+	int rc = AOF_OK;
+	if (!pipelined) rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, h->n, st);
 	else {
-		const int na = h->n / 2;
+		const int per = (h->n + parts - 1) / parts;
 		AOF_CUDA(cudaEventRecord(h->ev_fork, st));
-		AOF_CUDA(cudaStreamWaitEvent(h->st_aux, h->ev_fork, 0));
-		rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, na, st);
-		if (rc == AOF_OK) rc = run_range(h, nxt, d_t_us, d_out, d_raw, na, h->n - na, h->st_aux);
-		AOF_CUDA(cudaEventRecord(h->ev_join, h->st_aux));
+		AOF_CUDA(cudaStreamWaitEvent(h->st_hi, h->ev_fork, 0));
+		int np = 0;
+		for (int first = 0; first < h->n && rc == AOF_OK; first += per, np++) {
+			const int count = first + per <= h->n ? per : h->n - first;
+			rc = run_pyr_track(h, nxt, first, count, h->st_hi);
+			if (rc != AOF_OK) break;
+			AOF_CUDA(cudaEventRecord(h->ev_trk[np], h->st_hi));
+			AOF_CUDA(cudaStreamWaitEvent(h->st_lo, h->ev_trk[np], 0));
+			rc = run_fast(h, nxt, first, count, h->st_lo);
+			AOF_CUDA(cudaEventRecord(h->ev_fast[np], h->st_lo));
+		}
+		for (int first = 0, q = 0; first < h->n && rc == AOF_OK; first += per, q++) {
+			const int count = first + per <= h->n ? per : h->n - first;
+			AOF_CUDA(cudaStreamWaitEvent(h->st_hi, h->ev_fast[q], 0));
+			rc = run_select(h, d_t_us, d_out, d_raw, first, count, h->st_hi);
+		}
+		AOF_CUDA(cudaEventRecord(h->ev_join, h->st_hi));
 		AOF_CUDA(cudaStreamWaitEvent(st, h->ev_join, 0));
 	}
 	if (rc != AOF_OK) return rc;
@@ -320,11 +384,13 @@ int aof_lk_calc_flow_batch(aof_lk *h, const uint8_t *imgs, const uint32_t *t_us,
 	}
 	h->cur = nxt;
 	h->have_prev = h->have_feat_prev = true;
-	AOF_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
-	if (raw) AOF_CUDA(cudaMemcpyAsync(h->h_raw, h->d_raw, sizeof(aof_lk_raw) * h->n, cudaMemcpyDeviceToHost, h->st));
+	// the "host gather": straight into the caller's arrays when they are pinned (see aof_px4_calc_flow_batch)
+	const bool direct = host_pinned(out), direct_raw = raw && host_pinned(raw);
+	AOF_CUDA(cudaMemcpyAsync(direct ? out : h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
+	if (raw) AOF_CUDA(cudaMemcpyAsync(direct_raw ? raw : h->h_raw, h->d_raw, sizeof(aof_lk_raw) * h->n, cudaMemcpyDeviceToHost, h->st));
 	AOF_CUDA(cudaStreamSynchronize(h->st));
-	memcpy(out, h->h_out, sizeof(aof_flow_out) * h->n);
-	if (raw) memcpy(raw, h->h_raw, sizeof(aof_lk_raw) * h->n);
+	if (!direct) memcpy(out, h->h_out, sizeof(aof_flow_out) * h->n);
+	if (raw && !direct_raw) memcpy(raw, h->h_raw, sizeof(aof_lk_raw) * h->n);
 	return AOF_OK;
 }
 

@@ -81,6 +81,7 @@ int aof_px4_create(const aof_px4_params *p, int n_streams, int device, aof_px4 *
 	g.step = (hi - lo) / 5 + 1;
 	g.nb = 0;
 	for (int v = lo; v < hi; v += g.step) g.nb++;
+	g.tun_v1 = env_int("AOF_SAD_V1", 0); g.tun_v2 = env_int("AOF_SAD_V2", 0); g.tun_ctas = env_int("AOF_SAD_CTAS", 0);
 	g.feat_thr = (uint32_t)p->flow_feature_threshold;
 	g.val_thr = (uint32_t)p->flow_value_threshold;
 	cudaError_t e;
@@ -210,9 +211,12 @@ int aof_px4_calc_flow_batch(aof_px4 *h, const uint8_t *imgs, const uint32_t *t_u
 		}
 		h->d_prev = d_cur;
 	}
-	AOF_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
+	// the "host gather": 16 B per stream, straight into the caller's array when it is pinned (the multi-GPU entry
+	// points hand every device its slice of ONE pinned array), else through the handle's pinned buffer
+	const bool direct = host_pinned(out);
+	AOF_CUDA(cudaMemcpyAsync(direct ? out : h->h_out, h->d_out, sizeof(aof_flow_out) * h->n, cudaMemcpyDeviceToHost, h->st));
 	AOF_CUDA(cudaStreamSynchronize(h->st));
-	memcpy(out, h->h_out, sizeof(aof_flow_out) * h->n);
+	if (!direct) memcpy(out, h->h_out, sizeof(aof_flow_out) * h->n);
 	h->slot ^= 1;
 	return AOF_OK;
 }

@@ -236,8 +236,7 @@ static size_t fb_smem_bytes(const LkGeom &g, int &P, int &list_cap)
 
 bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0)
 {
-	const char *v1 = getenv("AOF_FAST_V1");
-	if (v1 && v1[0] == '1') return false;
+	if (g.tun_fast_v1 == 1) return false;
 	if (g.bw % 4 || g.w[0] % 4 || (reinterpret_cast<uintptr_t>(l0) & 3) || g.bh < 7 || g.bw < 8 || g.bw > 512) return false;
 	int P, cap;
 	return fb_smem_bytes(g, P, cap) <= 200 * 1024;

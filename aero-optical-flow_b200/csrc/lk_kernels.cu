@@ -540,9 +540,8 @@ cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkP
 				   int have_prev, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
-	static const bool v1 = getenv("AOF_TRACK_V1") && getenv("AOF_TRACK_V1")[0] == '1';
 	KernelTimer kt(KID_LK_TRACK_UPDATE, st);
-	if (v1) lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
+	if (g.tun_track_v1 == 1) lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
 	else {
 		const int groups = (g.n_feat + TS_WARPS - 1) / TS_WARPS;
 		lk_track_split_kernel<<<n * groups, TS_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev, groups);

@@ -432,8 +432,7 @@ bool lk_pyr_stream_supported(const LkGeom &g, const uint8_t *l0)
 // frames (no vertical cone recomputed) when it is large.  AOF_PYR_BANDS overrides (tuning).
 static int ps_bands(const LkGeom &g, int strips, int n)
 {
-	const char *e = getenv("AOF_PYR_BANDS");
-	const int forced = e ? atoi(e) : 0;
+	const int forced = g.tun_pyr_bands;
 	const int H3 = g.h[3];
 	int bands;
 	if (forced > 0) bands = forced;
@@ -458,11 +457,9 @@ cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1
 	const long long tasks = (long long)ss.n * bands * n;
 	if (tasks > 0x7FFFFFFFLL) return cudaErrorInvalidValue;
 	const unsigned blocks = (unsigned)((tasks + PS_WARPS - 1) / PS_WARPS);
-	const char *v1 = getenv("AOF_PYR_V1");
 	KernelTimer kt(KID_LK_PYR_FUSED, st);
-	const char *occ = getenv("AOF_PYR_OCC");
-	const int o = occ ? atoi(occ) : 16; // measured on B200: 16 CTAs/SM (<= 128 registers) is the fastest
-	if (g.h[0] % 16 == 0 && !(v1 && v1[0] == '1')) {
+	const int o = g.tun_pyr_occ > 0 ? g.tun_pyr_occ : 16; // measured on B200: 16 CTAs/SM (<= 128 registers) is the fastest
+	if (g.h[0] % 16 == 0 && g.tun_pyr_v1 != 1) {
 		if (o <= 16) lk_pyr_stream16_kernel<16><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 		else if (o <= 20) lk_pyr_stream16_kernel<20><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 		else lk_pyr_stream16_kernel<24><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);

@@ -292,15 +292,14 @@ static size_t sad2_dyn_smem(const SadGeom &g) { return (size_t)g.stage_bytes + 1
 
 bool sad_flow2_supported(const SadGeom &g)
 {
-	const char *v1 = getenv("AOF_SAD_V1");
-	if (v1 && v1[0] == '1') return false;
+	if (g.tun_v1 == 1) return false;
 	return sad2_dyn_smem(g) <= 200 * 1024;
 }
 
 template <int S> static cudaError_t launch_sad2(const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n,
 						aof_px4_raw *raw, aof_px4_block *blocks, cudaStream_t st)
 {
-	static int sms[64] = {};
+	static int sms[64] = {}, occ_dev[64] = {};
 	const size_t dyn = sad2_dyn_smem(g);
 	int dev = 0;
 	cudaGetDevice(&dev);
@@ -311,11 +310,16 @@ template <int S> static cudaError_t launch_sad2(const uint8_t *prev, const uint8
 		if ((e = cudaFuncSetAttribute(sad_flow2_kernel<S>, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess) return e;
 		if ((e = cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
 	}
-	int occ = 0;
-	if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sad_flow2_kernel<S>, 32, dyn)) != cudaSuccess) return e;
-	if (occ < 1) occ = 1;
-	const char *env = getenv("AOF_SAD_CTAS");
-	if (env && atoi(env) > 0 && atoi(env) < occ) occ = atoi(env);
+	// the occupancy query costs microseconds: once per device and frame size, not once per 30 us launch
+	static size_t occ_dyn[64] = {};
+	if (!occ_dev[dev] || occ_dyn[dev] != dyn) {
+		int q = 0;
+		if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, sad_flow2_kernel<S>, 32, dyn)) != cudaSuccess) return e;
+		occ_dev[dev] = q < 1 ? 1 : q;
+		occ_dyn[dev] = dyn;
+	}
+	int occ = occ_dev[dev];
+	if (g.tun_ctas > 0 && g.tun_ctas < occ) occ = g.tun_ctas;
 	long long grid = (long long)sms[dev] * occ;
 	if (grid > n) grid = n;
 	sad_flow2_kernel<S><<<(unsigned)grid, 32, dyn, st>>>(prev, cur, g, n, raw, blocks, 0x80000000u);

@@ -371,15 +371,14 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 // ---- host side -------------------------------------------------------------
 bool sad_flow3_supported(int search, const SadGeom &g)
 {
-	static const bool v2 = getenv("AOF_SAD_V2") && getenv("AOF_SAD_V2")[0] == '1'; // A/B switch, read once
-	return !v2 && search == S && g.width == W && g.stage_bytes == (uint32_t)(W * H) && g.nb == NB && g.lo == LO &&
+	return g.tun_v2 != 1 && g.tun_v1 != 1 && search == S && g.width == W && g.stage_bytes == (uint32_t)(W * H) && g.nb == NB && g.lo == LO &&
 	       g.step == STEP && AOF_PX4_MAX_BLOCKS == NBLK;
 }
 
 cudaError_t sad_flow3_launch(const uint8_t *prev, const uint8_t *cur, const SadGeom &g, int n, aof_px4_raw *raw,
 			     aof_px4_block *blocks, cudaStream_t st)
 {
-	static int grid_max[64] = {};
+	static int grid_max[64] = {}, sms_dev[64] = {};
 	int dev = 0;
 	cudaGetDevice(&dev);
 	if (dev >= 64) return cudaErrorInvalidDevice;
@@ -389,11 +388,12 @@ cudaError_t sad_flow3_launch(const uint8_t *prev, const uint8_t *cur, const SadG
 		if ((e = cudaFuncSetAttribute(sad_flow3_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess) return e;
 		if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
 		if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sad_flow3_kernel, 32, 0)) != cudaSuccess) return e;
-		const int cap = getenv("AOF_SAD_CTAS") ? atoi(getenv("AOF_SAD_CTAS")) : 0;
-		if (cap > 0 && cap < occ) occ = cap;
 		grid_max[dev] = sms * (occ < 1 ? 1 : occ);
+		sms_dev[dev] = sms;
 	}
-	const int grid = n < grid_max[dev] ? n : grid_max[dev];
+	int gmax = grid_max[dev];
+	if (g.tun_ctas > 0 && g.tun_ctas * sms_dev[dev] < gmax) gmax = g.tun_ctas * sms_dev[dev];
+	const int grid = n < gmax ? n : gmax;
 	sad_flow3_kernel<<<grid, 32, 0, st>>>(prev, cur, g.frame_stride, n, g.feat_thr, g.val_thr, raw, blocks, 0x80000000u);
 	return cudaGetLastError();
 }

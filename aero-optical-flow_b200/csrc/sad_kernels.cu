@@ -490,6 +490,7 @@ cudaError_t sad_flow_launch(int search, const uint8_t *prev, const uint8_t *cur,
 		count_launch();
 		return sad_flow3_launch(prev, cur, g, n, raw, blocks, st);
 	}
+	if (search != 4 && search != 6 && search != 8) return launch_sad_any(search, prev, cur, g, n, raw, blocks, st);
 	if (sad_flow2_supported(g)) {
 		KernelTimer kt(KID_SAD_FLOW, st);
 		count_launch();

@@ -166,6 +166,7 @@ typedef struct aof_lk aof_lk;
 int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **out);
 void aof_lk_destroy(aof_lk *h);
 int aof_lk_num_streams(const aof_lk *h);
+int aof_lk_num_features(const aof_lk *h);
 int aof_lk_reset(aof_lk *h);
 
 /* replaces OpticalFlowOpenCV::calcFlow (src/flow_opencv.cpp:89-210), 1-stream
@@ -211,6 +212,42 @@ int aof_lk_track_points(aof_lk *h, const uint8_t *prev, const uint8_t *cur, int 
 			float *next_pts, uint8_t *status);
 /* cv::FAST(bin ROI, 10, nonmax) on all 16 bins of n frames: score[n * w * h], 0 = no keypoint */
 int aof_lk_fast_scores(aof_lk *h, const uint8_t *imgs, int n, uint8_t *score);
+
+/* ------------------------------------------------------------------ multi-GPU */
+
+/* Both paths shard by whole streams: a stream's state is private and nothing is reduced across streams
+ * (src/flow_px4.cpp:69-98, src/flow_opencv.cpp:89-210), so the streams of a batch are partitioned over the GPUs of
+ * one box, each GPU owning a contiguous range of whole streams, with a host-side gather of the 16 B / stream results
+ * and no collective (no NCCL, no peer access).  A multi handle owns, per device, one single-device handle and one host
+ * worker thread (bound to the CPUs local to that GPU when the kernel exposes them); a batch call hands every worker
+ * its slice of the host frames, the worker runs aof_*_calc_flow_batch on its device (pinned staging, chunked
+ * asynchronous H2D under the kernels of the previous chunk) and its D2H lands in its slice of ONE pinned result
+ * array: that array is the gather.  devices[] are CUDA ordinals, all different; device i owns streams
+ * [first_i, first_i + count_i) with count_i = n_streams_total / n_devices (+ 1 for the first n_streams_total %
+ * n_devices devices).  Calls on one multi handle are serialised by the caller. */
+typedef struct aof_px4_multi aof_px4_multi;
+typedef struct aof_lk_multi aof_lk_multi;
+
+int aof_px4_create_multi(const aof_px4_params *p, int n_streams_total, const int *devices, int n_devices, aof_px4_multi **out);
+void aof_px4_destroy_multi(aof_px4_multi *m);
+/* imgs: n_streams_total frames back to back in HOST memory, t_us[n_streams_total].  out may be NULL (read the gathered
+ * results in place with aof_px4_multi_results) or n_streams_total entries, which receive a copy. */
+int aof_px4_multi_calc_flow_batch(aof_px4_multi *m, const uint8_t *imgs, const uint32_t *t_us, aof_flow_out *out);
+const aof_flow_out *aof_px4_multi_results(const aof_px4_multi *m);
+int aof_px4_multi_range(const aof_px4_multi *m, int i, int *device, int *first, int *count);
+int aof_px4_multi_set_params(aof_px4_multi *m, float focal_length_x, float focal_length_y, int output_rate);
+
+int aof_lk_create_multi(const aof_lk_params *p, int n_streams_total, const int *devices, int n_devices, aof_lk_multi **out);
+void aof_lk_destroy_multi(aof_lk_multi *m);
+/* raw may be NULL, aof_lk_multi_raw(m) itself (diagnostics gathered in place) or n_streams_total entries (copy) */
+int aof_lk_multi_calc_flow_batch(aof_lk_multi *m, const uint8_t *imgs, const uint32_t *t_us, aof_flow_out *out, aof_lk_raw *raw);
+const aof_flow_out *aof_lk_multi_results(const aof_lk_multi *m);
+const aof_lk_raw *aof_lk_multi_raw(const aof_lk_multi *m);
+int aof_lk_multi_range(const aof_lk_multi *m, int i, int *device, int *first, int *count);
+int aof_lk_multi_set_params(aof_lk_multi *m, float focal_length_x, float focal_length_y, int output_rate,
+			    float confidence_multiplier);
+/* state read-back for tests, all streams in global stream order (see aof_lk_get_state) */
+int aof_lk_multi_get_state(aof_lk_multi *m, int32_t *update_vec, float *feat_cur, float *prev_corners, uint8_t *prev_status);
 
 /* ------------------------------------------------------------ dense SAD field */
 

@@ -185,8 +185,9 @@ def test_any_search_size_vs_reference_objects(pkg, port, ref, s):
         assert (rq == 255).sum() >= 30          # the run is not vacuous
     else:
         assert (rq == 0).all()                  # 64 - 2 * 27 - 8 = 2 px of grid: one position, never > 10 votes
-    for i in (0, 17, 39):
-        check_blocks(port, prev[i], cur[i], blocks[i], s, 30, 3000)
+    if s <= 10:                                 # a full 5 x 5 grid: every block record is comparable
+        for i in (0, 17, 39):
+            check_blocks(port, prev[i], cur[i], blocks[i], s, 30, 3000)
     f.close()
 
 

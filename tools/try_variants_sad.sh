@@ -4,7 +4,7 @@ cp aero-optical-flow_b200/libaof_b200.so /tmp/keep.so
 for f in tmp_variants/lib_*.so; do
   cp $f aero-optical-flow_b200/libaof_b200.so
   for n in 4096 32768; do
-  AOF_BENCH_SAD_STREAMS=$n python bench.py --no-cpu --steps 300 --warmup 3 --workload sad 2>/dev/null | python -c "
+  AOF_BENCH_SAD_STREAMS=$n python bench.py --no-cpu --steps 300 --warmup 3 --workload sad 2>>gpurun_out/variants.err | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 k=[v for k,v in d['kernels'].items() if k.startswith('sad_flow')][0]
