@@ -7,4 +7,4 @@ makes deterministic test frames.  The directory name is not a Python identifier:
 load it with __graft_entry__.load_package() (module name `aof_b200`).
 """
 from . import capi, sharding, synth  # noqa: F401
-from .capi import AofError, Gftt, LkFlow, Px4Flow, SadDense, lib  # noqa: F401
+from .capi import AofError, Gftt, LkFlow, LkFlowMulti, Px4Flow, Px4FlowMulti, SadDense, lib  # noqa: F401

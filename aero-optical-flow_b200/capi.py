@@ -112,6 +112,27 @@ def lib():
     L.aof_gftt_destroy.restype = None
     L.aof_gftt_min_eig.argtypes = [vp, u8p, C.c_int, vp]
     L.aof_gftt_detect.argtypes = [vp, u8p, C.c_int, C.c_int, C.c_double, C.c_double, vp, vp]
+    L.aof_lk_lazy_stats.argtypes = [vp, C.POINTER(C.c_uint64)]
+    L.aof_lk_num_features.argtypes = [vp]
+    L.aof_px4_create_multi.argtypes = [C.POINTER(Px4Params), C.c_int, ip, C.c_int, C.POINTER(vp)]
+    L.aof_px4_destroy_multi.argtypes = [vp]
+    L.aof_px4_destroy_multi.restype = None
+    L.aof_px4_multi_calc_flow_batch.argtypes = [vp, u8p, u32p, vp]
+    L.aof_px4_multi_results.argtypes = [vp]
+    L.aof_px4_multi_results.restype = vp
+    L.aof_px4_multi_range.argtypes = [vp, C.c_int, ip, ip, ip]
+    L.aof_px4_multi_set_params.argtypes = [vp, C.c_float, C.c_float, C.c_int]
+    L.aof_lk_create_multi.argtypes = [C.POINTER(LkParams), C.c_int, ip, C.c_int, C.POINTER(vp)]
+    L.aof_lk_destroy_multi.argtypes = [vp]
+    L.aof_lk_destroy_multi.restype = None
+    L.aof_lk_multi_calc_flow_batch.argtypes = [vp, u8p, u32p, vp, vp]
+    L.aof_lk_multi_results.argtypes = [vp]
+    L.aof_lk_multi_results.restype = vp
+    L.aof_lk_multi_raw.argtypes = [vp]
+    L.aof_lk_multi_raw.restype = vp
+    L.aof_lk_multi_range.argtypes = [vp, C.c_int, ip, ip, ip]
+    L.aof_lk_multi_set_params.argtypes = [vp, C.c_float, C.c_float, C.c_int, C.c_float]
+    L.aof_lk_multi_get_state.argtypes = [vp, vp, vp, vp, vp]
     L.aof_host_register.argtypes = [vp, C.c_size_t]
     L.aof_host_unregister.argtypes = [vp]
     L.aof_crop_to_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
@@ -248,6 +269,12 @@ class LkFlow:
         """setFocalLengthX/Y, setOutputRate, setConfMultiplier on the live handle: all state is kept."""
         check(lib().aof_lk_set_params(self.handle, focal_x, focal_y, output_rate, conf_multi), "aof_lk_set_params")
 
+    def lazy_stats(self):
+        """(bins picked lazily, pool rebuilds, bins that overflowed, stream-frames sent to the complete path)"""
+        out = (C.c_uint64 * 4)()
+        check(lib().aof_lk_lazy_stats(self.handle, out), "aof_lk_lazy_stats")
+        return tuple(int(v) for v in out)
+
     def set_camera_matrix(self, fx, fy, cx, cy):
         check(lib().aof_lk_set_camera_matrix(self.handle, fx, fy, cx, cy), "aof_lk_set_camera_matrix")
 
@@ -297,6 +324,105 @@ class LkFlow:
         sc = np.zeros_like(imgs)
         check(lib().aof_lk_fast_scores(self.handle, _ptr(imgs), len(imgs), _ptr(sc)), "aof_lk_fast_scores")
         return sc
+
+
+class _Multi:
+    """Shared part of the multi-GPU wrappers: whole streams per device, one host worker thread per device inside the
+    library, results gathered into ONE pinned host array (no collective)."""
+    _kind = None
+
+    def _devs(self, devices):
+        devices = list(range(lib().aof_device_count())) if devices is None else list(devices)
+        return devices, (C.c_int * len(devices))(*devices)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            getattr(lib(), "aof_%s_destroy_multi" % self._kind)(self.handle)
+            self.handle = None
+
+    __del__ = close
+
+    def ranges(self):
+        """[(device, first stream, stream count)] -- the shard of each device"""
+        out = []
+        for i in range(self.n_devices):
+            d, f, c = C.c_int(), C.c_int(), C.c_int()
+            check(getattr(lib(), "aof_%s_multi_range" % self._kind)(self.handle, i, C.byref(d), C.byref(f), C.byref(c)), "multi_range")
+            out.append((d.value, f.value, c.value))
+        return out
+
+    def _view(self, addr, dtype):
+        buf = (C.c_char * (self.n * dtype.itemsize)).from_address(addr)
+        return np.frombuffer(buf, dtype=dtype, count=self.n)
+
+
+class Px4FlowMulti(_Multi):
+    """n_streams OpticalFlowPX4 instances sharded over `devices` (default: all) -- aof_px4_create_multi."""
+    _kind = "px4"
+
+    def __init__(self, focal_x, focal_y, output_rate=15, width=64, height=64, search=6, feat_thr=30, val_thr=3000,
+                 n_streams=1, devices=None):
+        L = lib()
+        self.params = Px4Params(focal_x, focal_y, output_rate, width, height, search, feat_thr, val_thr)
+        self.n, self.w, self.h = n_streams, width, height
+        devs, arr = self._devs(devices)
+        self.n_devices = len(devs)
+        self.handle = C.c_void_p()
+        check(L.aof_px4_create_multi(C.byref(self.params), n_streams, arr, len(devs), C.byref(self.handle)), "aof_px4_create_multi")
+
+    def calc_flow_batch(self, imgs, t_us, copy=True):
+        """imgs: n_streams frames in host memory (pinned for full speed).  copy=False returns a view of the library's
+        pinned result array (valid until the next call)."""
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        t_us = np.ascontiguousarray(t_us, np.uint32)
+        assert imgs.size == self.n * self.w * self.h and t_us.size == self.n
+        check(lib().aof_px4_multi_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), None), "aof_px4_multi_calc_flow_batch")
+        v = self._view(lib().aof_px4_multi_results(self.handle), flow_out_dtype)
+        return v.copy() if copy else v
+
+    def set_params(self, focal_x, focal_y, output_rate):
+        check(lib().aof_px4_multi_set_params(self.handle, focal_x, focal_y, output_rate), "aof_px4_multi_set_params")
+
+
+class LkFlowMulti(_Multi):
+    """n_streams OpticalFlowOpenCV instances sharded over `devices` (default: all) -- aof_lk_create_multi."""
+    _kind = "lk"
+
+    def __init__(self, focal_x, focal_y, output_rate=15, width=64, height=64, num_features=20, conf_multi=1.645,
+                 n_streams=1, devices=None):
+        L = lib()
+        self.params = LkParams(focal_x, focal_y, output_rate, width, height, num_features, conf_multi)
+        self.n, self.w, self.h, self.nf = n_streams, width, height, num_features
+        devs, arr = self._devs(devices)
+        self.n_devices = len(devs)
+        self.handle = C.c_void_p()
+        check(L.aof_lk_create_multi(C.byref(self.params), n_streams, arr, len(devs), C.byref(self.handle)), "aof_lk_create_multi")
+
+    def calc_flow_batch(self, imgs, t_us, want_raw=False, copy=True):
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        t_us = np.ascontiguousarray(t_us, np.uint32)
+        assert imgs.size == self.n * self.w * self.h and t_us.size == self.n
+        L = lib()
+        raw_addr = L.aof_lk_multi_raw(self.handle)
+        check(L.aof_lk_multi_calc_flow_batch(self.handle, _ptr(imgs), _ptr(t_us), None, raw_addr if want_raw else None),
+              "aof_lk_multi_calc_flow_batch")
+        out = self._view(L.aof_lk_multi_results(self.handle), flow_out_dtype)
+        out = out.copy() if copy else out
+        if not want_raw:
+            return out
+        raw = self._view(raw_addr, lk_raw_dtype)
+        return out, (raw.copy() if copy else raw)
+
+    def set_params(self, focal_x, focal_y, output_rate, conf_multi):
+        check(lib().aof_lk_multi_set_params(self.handle, focal_x, focal_y, output_rate, conf_multi), "aof_lk_multi_set_params")
+
+    def state(self):
+        uv = np.zeros((self.n, self.nf), np.int32)
+        fc = np.zeros((self.n, self.nf, 2), np.float32)
+        pc = np.zeros((self.n, self.nf, 2), np.float32)
+        ps = np.zeros((self.n, self.nf), np.uint8)
+        check(lib().aof_lk_multi_get_state(self.handle, _ptr(uv), _ptr(fc), _ptr(pc), _ptr(ps)), "aof_lk_multi_get_state")
+        return {"update_vec": uv, "feat_cur": fc, "prev_corners": pc, "prev_status": ps}
 
 
 class SadDense:

@@ -75,10 +75,12 @@ int stage_h2d(void *d_dst, const void *src, size_t bytes, void *stage, cudaStrea
 // time to its kernels and by whoever wants a trace without a profiler.
 namespace aof {
 
-static const char *const g_kernel_names[KID_COUNT] = {
+// slot -> kernel symbol.  The entries below are the defaults; a launch wrapper that picks among several kernels passes
+// the symbol of the one it launches to KernelTimer, which records it here, so that the timing table names what ran.
+static const char *g_kernel_names[KID_COUNT] = {
 	"sad_flow_kernel", "px4_epilogue_kernel", "lk_pyr_down_kernel", "lk_track_update_kernel", "lk_fast_kernel",
 	"lk_select_epilogue_kernel", "lk_track_points_kernel", "sad_dense_kernel", "gftt_min_eig_kernel", "gftt_select_kernel",
-	"lk_pyr_fused_kernel",
+	"lk_pyr_fused_kernel", "lk_fast_pick_kernel", "lk_fast_band_flagged_kernel",
 };
 
 struct TimingState {
@@ -94,10 +96,11 @@ static std::atomic<bool> g_timing_on{false};
 
 bool timing_on() { return g_timing_on.load(std::memory_order_relaxed); }
 
-KernelTimer::KernelTimer(int kid, cudaStream_t st) : kid_(kid), st_(st)
+KernelTimer::KernelTimer(int kid, cudaStream_t st, const char *symbol) : kid_(kid), st_(st)
 {
 	if (!g_timing_on.load(std::memory_order_relaxed)) return;
 	std::lock_guard<std::mutex> lk(g_t.mu);
+	if (symbol) g_kernel_names[kid] = symbol;
 	TimingState::Pair p;
 	if (!g_t.pool.empty()) { p = g_t.pool.back(); g_t.pool.pop_back(); }
 	else if (cudaEventCreate(&p.a) != cudaSuccess || cudaEventCreate(&p.b) != cudaSuccess) return;

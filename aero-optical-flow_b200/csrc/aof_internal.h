@@ -70,7 +70,7 @@ void count_launch(uint64_t n = 1);
 // kernel ids of the optional per-kernel event timing (aof_timing_* in include/aof.h)
 enum KernelId {
 	KID_SAD_FLOW = 0, KID_PX4_EPILOGUE, KID_LK_PYR_DOWN, KID_LK_TRACK_UPDATE, KID_LK_FAST, KID_LK_SELECT_EPILOGUE,
-	KID_LK_TRACK_POINTS, KID_SAD_DENSE, KID_GFTT_MIN_EIG, KID_GFTT_SELECT, KID_LK_PYR_FUSED, KID_COUNT
+	KID_LK_TRACK_POINTS, KID_SAD_DENSE, KID_GFTT_MIN_EIG, KID_GFTT_SELECT, KID_LK_PYR_FUSED, KID_LK_FAST_PICK, KID_LK_FAST_FLAGGED, KID_COUNT
 };
 
 // brackets one launch with two events when timing is enabled; a no-op otherwise
@@ -78,7 +78,8 @@ bool timing_on(); // per-kernel event timing requested (aof_timing_enable)
 
 class KernelTimer {
 public:
-	KernelTimer(int kid, cudaStream_t st);
+	// `symbol`: the __global__ function this launch runs (what a profiler lists); aof_timing_read reports it for the slot
+	KernelTimer(int kid, cudaStream_t st, const char *symbol = nullptr);
 	~KernelTimer();
 private:
 	int kid_;
@@ -110,6 +111,7 @@ constexpr int LK_MAX_LEVELS = 4;   // maxLevel = 3 (trackFeatures.cpp:98)
 constexpr int LK_WIN = 9;          // Size(9, 9)
 constexpr int LK_MAX_FEATURES = 100; // trackFeatures.cpp:56
 constexpr int LK_BINS = 16;        // 4 x 4 (trackFeatures.cpp:156-157)
+constexpr int LK_MAX_TPB = (LK_MAX_FEATURES - 1) / LK_BINS + 1; // targetFeaturesPerBin <= 7
 
 struct LkGeom {
 	int w[LK_MAX_LEVELS], h[LK_MAX_LEVELS];
@@ -126,6 +128,7 @@ struct LkGeom {
 	int tun_pyr_v1;    // AOF_PYR_V1 = 1: the generic streaming kernel
 	int tun_fast_v1;   // AOF_FAST_V1 = 1: the tile FAST kernel
 	int tun_track_v1;  // AOF_TRACK_V1 = 1: the CTA-per-stream tracker
+	int tun_fast_lazy; // AOF_FAST_LAZY = 0: always score every pixel of the needed bins (default 1: lazy FAST)
 };
 
 // level base pointers of one pyramid slot; level l of stream s is at lvl[l] + s * w[l] * h[l]
@@ -149,6 +152,15 @@ struct LkState {
 	float2 *lk_next;        // [n * N]   LK result per slot, handed from the tracking CTAs to the bookkeeping CTA
 	uint8_t *lk_stat;       // [n * N]
 	int *ticket;            // [n]       tracking CTAs of the stream that have finished (0 between launches)
+	// lazy FAST (lk_fast_lazy.cu): the per-bin picks of initMorePoints' first stage, found without scoring every pixel
+	uint32_t *lz_pick;      // [n * 16 * LK_MAX_TPB]  x | y << 16 (image coordinates), in pick order
+	int *lz_npick;          // [n * 16]
+	int *lz_floor;          // [n * 16]  adaptive pool threshold of the bin (persistent; 0 = not yet set)
+	int *need_full;         // [n]       1 = the selection needs the complete keypoint lists of this stream (second chance)
+	int *n_full;            // [n]       element 0 of a range counts its flagged streams (reset by the fallback selection)
+	int *full_list;         // [n]       range-local indices of the flagged streams
+	unsigned long long *lz_stats; // [4] diagnostics, whole handle: bins picked lazily, pool rebuilds, bins that overflowed
+	                              //     the lazy buffers, streams sent to the complete path
 };
 
 // camera model of setCameraMatrix / setCameraDistortion (flow_opencv.cpp:72-87); on only when both were set
@@ -170,9 +182,17 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 // banded FAST (lk_fast_band.cu); lk_fast_launch dispatches to it when the shape allows
 bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0);
 cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st);
+// the same for the streams listed in s.full_list only (small persistent grid)
+cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);
+// lazy FAST (lk_fast_lazy.cu): the per-bin picks of initMorePoints without scoring every pixel
+bool lk_fast_lazy_supported(const LkGeom &g, const uint8_t *l0);
+cudaError_t lk_fast_pick_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);
+// mode of lk_select_epilogue_launch: the complete path; the picks of lk_fast_pick_kernel (flags the streams that need
+// the complete path and leaves them untouched); the complete path for the flagged streams only
+enum { LK_SEL_COMPLETE = 0, LK_SEL_LAZY = 1, LK_SEL_FLAGGED = 2 };
 cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
 				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
-				      float fy, const LkCamera &cam, cudaStream_t st);
+				      float fy, const LkCamera &cam, cudaStream_t st, int mode = LK_SEL_COMPLETE);
 // stateless pyramidal LK over given points (KAT entry): pts[n * n_pts]
 cudaError_t lk_track_points_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const float2 *pts, int n_pts,
 				   float2 *out, uint8_t *status, int n, cudaStream_t st);

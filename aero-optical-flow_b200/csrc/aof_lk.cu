@@ -63,6 +63,8 @@ static LkState state_from(const LkState &s, const LkGeom &g, size_t first)
 	v.feat_cur += first * N; v.feat_prev += first * N; v.lim += first; v.bin_needed += first * LK_BINS; v.target += first;
 	v.kp_count += first * LK_BINS; v.kp += first * LK_BINS * (size_t)g.kp_cap;
 	v.lk_next += first * N; v.lk_stat += first * N; v.ticket += first;
+	v.lz_pick += first * LK_BINS * LK_MAX_TPB; v.lz_npick += first * LK_BINS; v.lz_floor += first * LK_BINS;
+	v.need_full += first; v.n_full += first; v.full_list += first;
 	return v;
 }
 
@@ -94,6 +96,11 @@ static int reset_state(aof_lk *h)
 	AOF_CUDA(cudaMemset(h->s.target, 0, sizeof(int) * h->n));
 	AOF_CUDA(cudaMemset(h->s.kp_count, 0, sizeof(int) * LK_BINS * h->n));
 	AOF_CUDA(cudaMemset(h->s.ticket, 0, sizeof(int) * h->n));
+	AOF_CUDA(cudaMemset(h->s.lz_npick, 0, sizeof(int) * LK_BINS * h->n));
+	AOF_CUDA(cudaMemset(h->s.lz_floor, 0, sizeof(int) * LK_BINS * h->n));
+	AOF_CUDA(cudaMemset(h->s.need_full, 0, sizeof(int) * h->n));
+	AOF_CUDA(cudaMemset(h->s.n_full, 0, sizeof(int) * h->n));
+	AOF_CUDA(cudaMemset(h->s.lz_stats, 0, sizeof(unsigned long long) * 4));
 	h->have_prev = h->have_feat_prev = false;
 	h->cur = 0;
 	h->l0[0] = h->l0[1] = nullptr;
@@ -156,6 +163,7 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	const size_t nN = (size_t)n_streams * N;
 	// every environment switch of this path is read here, once (never on a launch path)
 	g.tun_pyr_bands = env_int("AOF_PYR_BANDS", 0); g.tun_pyr_occ = env_int("AOF_PYR_OCC", 0);
+	g.tun_fast_lazy = env_int("AOF_FAST_LAZY", 1);
 	g.tun_pyr_v1 = env_int("AOF_PYR_V1", 0); g.tun_fast_v1 = env_int("AOF_FAST_V1", 0); g.tun_track_v1 = env_int("AOF_TRACK_V1", 0);
 	h->tun_split = env_int("AOF_LK_SPLIT", 0); h->tun_parts = env_int("AOF_LK_PARTS", 0);
 	cudaError_t e;
@@ -190,6 +198,13 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	    (e = cudaMalloc(&h->s.lk_next, sizeof(float2) * nN)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.lk_stat, nN)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.ticket, sizeof(int) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lz_pick, sizeof(uint32_t) * LK_BINS * LK_MAX_TPB * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lz_npick, sizeof(int) * LK_BINS * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lz_floor, sizeof(int) * LK_BINS * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.need_full, sizeof(int) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.n_full, sizeof(int) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.full_list, sizeof(int) * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.lz_stats, sizeof(unsigned long long) * 4)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.kp, sizeof(uint32_t) * LK_BINS * (size_t)g.kp_cap * n_streams)) != cudaSuccess) {
 		set_error("aof_lk_create: %s", cudaGetErrorString(e));
 		aof_lk_destroy(h);
@@ -211,6 +226,8 @@ void aof_lk_destroy(aof_lk *h)
 	cudaFree(h->s.feat_cur); cudaFree(h->s.feat_prev); cudaFree(h->s.lim); cudaFree(h->s.bin_needed);
 	cudaFree(h->s.target); cudaFree(h->s.kp_count); cudaFree(h->s.kp);
 	cudaFree(h->s.lk_next); cudaFree(h->s.lk_stat); cudaFree(h->s.ticket);
+	cudaFree(h->s.lz_pick); cudaFree(h->s.lz_npick); cudaFree(h->s.lz_floor);
+	cudaFree(h->s.need_full); cudaFree(h->s.n_full); cudaFree(h->s.full_list); cudaFree(h->s.lz_stats);
 	cudaFree(h->d_frames[0]); cudaFree(h->d_frames[1]);
 	cudaFreeHost(h->h_stage); cudaFreeHost(h->h_t); cudaFreeHost(h->h_out); cudaFreeHost(h->h_raw);
 	cudaFree(h->d_t); cudaFree(h->d_out); cudaFree(h->d_raw);
@@ -231,6 +248,17 @@ void aof_lk_destroy(aof_lk *h)
 
 int aof_lk_num_streams(const aof_lk *h) { return h ? h->n : AOF_ERR_INVALID; }
 int aof_lk_num_features(const aof_lk *h) { return h ? h->g.n_feat : AOF_ERR_INVALID; }
+
+int aof_lk_lazy_stats(aof_lk *h, uint64_t out[4])
+{
+	if (!h || !out) return AOF_ERR_INVALID;
+	AOF_CUDA(cudaSetDevice(h->device));
+	AOF_CUDA(cudaDeviceSynchronize());
+	unsigned long long v[4];
+	AOF_CUDA(cudaMemcpy(v, h->s.lz_stats, sizeof v, cudaMemcpyDeviceToHost));
+	for (int i = 0; i < 4; i++) out[i] = v[i];
+	return AOF_OK;
+}
 
 int aof_lk_reset(aof_lk *h)
 {
@@ -261,10 +289,13 @@ static int run_pyr_track(aof_lk *h, int nxt, int first, int count, cudaStream_t 
 	return AOF_OK;
 }
 
+// lazy FAST (lk_fast_lazy.cu) where the shape allows, else the complete keypoint lists
 static int run_fast(aof_lk *h, int nxt, int first, int count, cudaStream_t st)
 {
 	const size_t f = (size_t)first;
-	AOF_CUDA(lk_fast_launch(h->g, pyr_of(h, nxt, f).lvl[0], state_from(h->s, h->g, f), count, nullptr, st));
+	const uint8_t *l0 = pyr_of(h, nxt, f).lvl[0];
+	if (lk_fast_lazy_supported(h->g, l0)) AOF_CUDA(lk_fast_pick_launch(h->g, l0, state_from(h->s, h->g, f), count, st));
+	else AOF_CUDA(lk_fast_launch(h->g, l0, state_from(h->s, h->g, f), count, nullptr, st));
 	return AOF_OK;
 }
 
@@ -272,9 +303,18 @@ static int run_select(aof_lk *h, const uint32_t *d_t_us, aof_flow_out *d_out, ao
 		      cudaStream_t st)
 {
 	const size_t f = (size_t)first;
-	AOF_CUDA(lk_select_epilogue_launch(h->g, state_from(h->s, h->g, f), d_t_us + f, d_out + f, d_raw ? d_raw + f : nullptr, count,
-					   h->have_feat_prev ? 1 : 0, h->p.output_rate, h->p.confidence_multiplier,
-					   h->p.focal_length_x, h->p.focal_length_y, h->cam, st));
+	const LkState sv = state_from(h->s, h->g, f);
+	const uint8_t *l0 = pyr_of(h, h->cur ^ 1, f).lvl[0];
+	const bool lazy = lk_fast_lazy_supported(h->g, l0);
+	// lazy: the selection takes the picks, flags the streams whose second-chance pass needs every keypoint; those (usually
+	// none) then go through the complete FAST and the complete selection
+	for (int pass = 0; pass < (lazy ? 2 : 1); pass++) {
+		if (pass == 1) AOF_CUDA(lk_fast_band_flagged_launch(h->g, l0, sv, count, st));
+		AOF_CUDA(lk_select_epilogue_launch(h->g, sv, d_t_us + f, d_out + f, d_raw ? d_raw + f : nullptr, count,
+						   h->have_feat_prev ? 1 : 0, h->p.output_rate, h->p.confidence_multiplier,
+						   h->p.focal_length_x, h->p.focal_length_y, h->cam, st,
+						   !lazy ? LK_SEL_COMPLETE : pass == 0 ? LK_SEL_LAZY : LK_SEL_FLAGGED));
+	}
 	return AOF_OK;
 }
 

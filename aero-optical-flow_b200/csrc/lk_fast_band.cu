@@ -81,9 +81,8 @@ __device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint3
 // PC = row pitch of the shared-memory arrays in words when it is known at compile time (84 for the 160-px bins of a
 // 640-px frame: every ring tap is then an immediate offset of one base address), 0 = run time (P_rt)
 template <int THREADS, int PC>
-__global__ void __launch_bounds__(THREADS, 1280 / THREADS)
-lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
-		    int list_cap)
+__device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restrict__ l0, const LkState &s, uint8_t *__restrict__ score_map,
+					 int bands, int P_rt, int list_cap, size_t stream, int bin, int band)
 {
 	const int P = PC ? PC : P_rt;
 	extern __shared__ __align__(16) uint32_t fb_smem[];
@@ -93,8 +92,6 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	uint32_t *sL = sS + FB_SROWS * P;
 	__shared__ int s_n, s_base;
 
-	const size_t stream = blockIdx.y;
-	const int bin = blockIdx.x / bands, band = blockIdx.x - bin * bands;
 	if (!score_map && s.bin_needed[stream * LK_BINS + bin] == 0) return;
 	const int W = g.w[0], H = g.h[0], bh = g.bh;
 	const int bw = PC ? (PC - 4) * 2 : g.bw;                      // compile-time bin width: the index arithmetic below folds
@@ -225,6 +222,32 @@ lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t
 	}
 }
 
+// one CTA per (stream, bin, band)
+template <int THREADS, int PC>
+__global__ void __launch_bounds__(THREADS, 1280 / THREADS)
+lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
+		    int list_cap)
+{
+	const int bin = blockIdx.x / bands;
+	fb_body<THREADS, PC>(g, l0, s, score_map, bands, P_rt, list_cap, blockIdx.y, bin, blockIdx.x - bin * bands);
+}
+
+// The complete keypoint lists of the FLAGGED streams only (lazy FAST, lk_fast_lazy.cu: the selection kernel lists the
+// streams whose second-chance pass needs every keypoint in s.full_list / s.n_full[0]).  A small persistent grid walks
+// over (flagged stream, bin, band): with nothing flagged -- the usual case -- the launch costs a few microseconds.
+template <int THREADS, int PC>
+__global__ void __launch_bounds__(THREADS, 1280 / THREADS)
+lk_fast_band_flagged_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, int bands, int P_rt, int list_cap)
+{
+	const int n_flag = s.n_full[0];
+	const int per_stream = LK_BINS * bands;
+	for (int w = blockIdx.x; w < n_flag * per_stream; w += gridDim.x) {
+		const int f = w / per_stream, r = w - f * per_stream, bin = r / bands;
+		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)s.full_list[f], bin, r - bin * bands);
+		__syncthreads();                                    // the next item reuses the shared-memory tiles and counters
+	}
+}
+
 // ---- host side -------------------------------------------------------------
 static size_t fb_smem_bytes(const LkGeom &g, int &P, int &list_cap)
 {
@@ -259,6 +282,41 @@ static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &
 	dim3 grid(LK_BINS * bands, n);
 	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
 	return cudaGetLastError();
+}
+
+template <int THREADS, int PC>
+static cudaError_t fb_launch_flagged(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st)
+{
+	int P, cap;
+	const size_t smem = fb_smem_bytes(g, P, cap);
+	static int grid_dev[64] = {};
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev >= 64) return cudaErrorInvalidDevice;
+	if (!grid_dev[dev]) {
+		cudaError_t e = cudaFuncSetAttribute(lk_fast_band_flagged_kernel<THREADS, PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+		if (e != cudaSuccess) return e;
+		int sms = 0;
+		if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+		grid_dev[dev] = sms * (1280 / THREADS);
+	}
+	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
+	long long items = (long long)n * LK_BINS * bands;
+	const int grid = (int)(items < grid_dev[dev] ? items : grid_dev[dev]);
+	lk_fast_band_flagged_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, bands, P, cap);
+	return cudaGetLastError();
+}
+
+cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st)
+{
+	if (n <= 0) return cudaSuccess;
+	const int npc = g.bw / 2;
+	KernelTimer kt(KID_LK_FAST_FLAGGED, st, npc == 80 ? "lk_fast_band_flagged_kernel<320,84>" : "lk_fast_band_flagged_kernel");
+	count_launch();
+	if (npc == 80) return fb_launch_flagged<320, 84>(g, l0, s, n, st);
+	if (4 * npc <= 320) return fb_launch_flagged<320, 0>(g, l0, s, n, st);
+	if (4 * npc <= 640) return fb_launch_flagged<640, 0>(g, l0, s, n, st);
+	return fb_launch_flagged<1024, 0>(g, l0, s, n, st);
 }
 
 cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)

@@ -177,7 +177,7 @@ cudaError_t lk_pyr_fused_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1,
 {
 	if (n <= 0) return cudaSuccess;
 	dim3 grid((g.w[3] + PF3W - 1) / PF3W, (g.h[3] + PF3H - 1) / PF3H, n);
-	KernelTimer kt(KID_LK_PYR_FUSED, st);
+	KernelTimer kt(KID_LK_PYR_FUSED, st, "lk_pyr_fused_kernel");
 	if (g.w[0] % 4 == 0 && (reinterpret_cast<uintptr_t>(l0) & 3) == 0 && ((size_t)g.w[0] * g.h[0]) % 4 == 0)
 		lk_pyr_fused_kernel<true><<<grid, PF_THREADS, 0, st>>>(g, l0, l1, l2, l3);
 	else
@@ -540,7 +540,7 @@ cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkP
 				   int have_prev, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
-	KernelTimer kt(KID_LK_TRACK_UPDATE, st);
+	KernelTimer kt(KID_LK_TRACK_UPDATE, st, g.tun_track_v1 == 1 ? "lk_track_update_kernel" : "lk_track_split_kernel");
 	if (g.tun_track_v1 == 1) lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
 	else {
 		const int groups = (g.n_feat + TS_WARPS - 1) / TS_WARPS;
@@ -707,8 +707,9 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 	if (n <= 0) return cudaSuccess;
 	const int tiles_x = (g.bw + FT_TW - 1) / FT_TW, tiles_y = (g.bh + FT_TH - 1) / FT_TH;
 	dim3 grid(tiles_x * tiles_y * LK_BINS, n);
-	KernelTimer kt(KID_LK_FAST, st);
-	if (lk_fast_band_supported(g, l0)) {
+	const bool band = lk_fast_band_supported(g, l0);
+	KernelTimer kt(KID_LK_FAST, st, !band ? "lk_fast_kernel" : g.bw == 160 ? "lk_fast_band_kernel<320,84>" : "lk_fast_band_kernel");
+	if (band) {
 		count_launch();
 		return lk_fast_band_launch(g, l0, s, n, score_map, st);
 	}
@@ -734,7 +735,7 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 #define AOF_SEL_THREADS 256
 #endif
 constexpr int SEL_THREADS = AOF_SEL_THREADS;
-constexpr int SEL_MAX_TPB = (LK_MAX_FEATURES - 1) / LK_BINS + 1; // 7
+constexpr int SEL_MAX_TPB = LK_MAX_TPB;
 constexpr int SEL_MAX_GOOD = LK_BINS * SEL_MAX_TPB + LK_MAX_FEATURES;
 constexpr int SEL_STAGE = 8192 / (SEL_THREADS / 32);          // keypoints of a bin staged in shared memory (32 KB per CTA)
 
@@ -767,7 +768,7 @@ __device__ float2 lk_undistort(const LkCamera &c, float2 pt)
 __global__ void __launch_bounds__(SEL_THREADS)
 lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us, aof_flow_out *__restrict__ out,
 			  aof_lk_raw *__restrict__ raw, int have_feat_prev, int output_rate, float conf, float focal_x,
-			  float focal_y, LkCamera cam)
+			  float focal_y, LkCamera cam, int mode)
 {
 	__shared__ int s_ex[LK_MAX_FEATURES], s_ey[LK_MAX_FEATURES];
 	__shared__ int s_nex, s_ngood, s_done;
@@ -780,6 +781,11 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 	const size_t stream = blockIdx.x;
 	const int N = g.n_feat, W = g.w[0];
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	// LK_SEL_FLAGGED: the complete path for the streams the lazy pass flagged, nothing for the others
+	if (mode == LK_SEL_FLAGGED) {
+		if (blockIdx.x == 0 && tid == 0) s.n_full[0] = 0;      // the flagged FAST launch before this one has consumed it
+		if (!s.need_full[stream]) return;
+	}
 	float2 *pc = s.prev_corners + stream * N;
 	uint8_t *ps = s.prev_status + stream * N;
 	int *uv = s.update_vec + stream * N;
@@ -792,7 +798,8 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 	__shared__ float2 s_pc[LK_MAX_FEATURES], s_fc[LK_MAX_FEATURES], s_fp[LK_MAX_FEATURES];
 	__shared__ int s_uv[LK_MAX_FEATURES];
 	__shared__ uint8_t s_ps[LK_MAX_FEATURES];
-	__shared__ int s_fast_bins;
+	__shared__ int s_fast_bins, s_lazy_fail;
+	if (tid == 0) s_lazy_fail = 0;
 	for (int i = tid; i < N; i += SEL_THREADS) { s_pc[i] = pc[i]; s_fc[i] = fc[i]; s_fp[i] = fp[i]; s_uv[i] = uv[i]; s_ps[i] = ps[i]; }
 	__syncthreads();
 
@@ -811,8 +818,19 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 		}
 		__syncthreads();
 		const int nex = s_nex;
+		// ---- stage 1 with the picks of lk_fast_pick_kernel (lazy FAST): they ARE what the loop below would find
+		if (mode == LK_SEL_LAZY && tid < LK_BINS) {
+			const int b = tid;
+			int np = s_needed[b] > 0 ? s.lz_npick[stream * LK_BINS + b] : 0;
+			if (np < 0) { s_lazy_fail = 1; np = 0; }           // the bin overflowed the lazy kernel's buffers
+			for (int j = 0; j < np; j++) {
+				const uint32_t e = s.lz_pick[(stream * LK_BINS + b) * LK_MAX_TPB + j];
+				s_px[b][j] = (int)(e & 0xFFFFu); s_py[b][j] = (int)(e >> 16);
+			}
+			s_npick[b] = np;
+		}
 		// ---- stage 1: one warp per bin
-		for (int b = warp; b < LK_BINS; b += SEL_THREADS / 32) {
+		for (int b = warp; b < LK_BINS && mode != LK_SEL_LAZY; b += SEL_THREADS / 32) {
 			if (s_needed[b] <= 0) continue;
 			const int needed = s_needed[b], cnt = s_cnt[b];
 			const int c0 = (b >> 2) * g.bw, r0 = (b & 3) * g.bh;
@@ -909,6 +927,16 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 			}
 		}
 		__syncthreads();
+		if (mode == LK_SEL_LAZY && (!s_done || s_lazy_fail)) {
+			// the second-chance pass needs every keypoint of every processed bin: hand the stream to the complete path
+			// (lk_fast_band_flagged_kernel, then this kernel in LK_SEL_FLAGGED mode); no state has been written yet
+			if (tid == 0) {
+				s.need_full[stream] = 1;
+				atomicAdd(&s.lz_stats[3], 1ull);
+				s.full_list[atomicAdd(&s.n_full[0], 1)] = (int)blockIdx.x;
+			}
+			return;
+		}
 		// ---- stage 3: second chance over every keypoint of the processed bins at dist / 2
 		const int dist2 = g.dist / 2;
 		while (!s_done) {
@@ -1027,6 +1055,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 		}
 	}
 	__syncthreads();
+	if (mode == LK_SEL_FLAGGED && tid == 0) s.need_full[stream] = 0;
 	// features_previous = features_current; status machine (flow_opencv.cpp:183-196); write the state back
 	for (int i = tid; i < N; i += SEL_THREADS) {
 		int u = s_uv[i];
@@ -1042,11 +1071,11 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 
 cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
 				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
-				      float fy, const LkCamera &cam, cudaStream_t st)
+				      float fy, const LkCamera &cam, cudaStream_t st, int mode)
 {
 	if (n <= 0) return cudaSuccess;
 	KernelTimer kt(KID_LK_SELECT_EPILOGUE, st);
-	lk_select_epilogue_kernel<<<n, SEL_THREADS, 0, st>>>(g, s, t_us, out, raw, have_feat_prev, output_rate, conf, fx, fy, cam);
+	lk_select_epilogue_kernel<<<n, SEL_THREADS, 0, st>>>(g, s, t_us, out, raw, have_feat_prev, output_rate, conf, fx, fy, cam, mode);
 	count_launch();
 	return cudaGetLastError();
 }

@@ -457,9 +457,10 @@ cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1
 	const long long tasks = (long long)ss.n * bands * n;
 	if (tasks > 0x7FFFFFFFLL) return cudaErrorInvalidValue;
 	const unsigned blocks = (unsigned)((tasks + PS_WARPS - 1) / PS_WARPS);
-	KernelTimer kt(KID_LK_PYR_FUSED, st);
+	const bool rows16 = g.h[0] % 16 == 0 && g.tun_pyr_v1 != 1;
 	const int o = g.tun_pyr_occ > 0 ? g.tun_pyr_occ : 16; // measured on B200: 16 CTAs/SM (<= 128 registers) is the fastest
-	if (g.h[0] % 16 == 0 && g.tun_pyr_v1 != 1) {
+	KernelTimer kt(KID_LK_PYR_FUSED, st, !rows16 ? "lk_pyr_stream_kernel" : o <= 16 ? "lk_pyr_stream16_kernel<16>" : o <= 20 ? "lk_pyr_stream16_kernel<20>" : "lk_pyr_stream16_kernel<24>");
+	if (rows16) {
 		if (o <= 16) lk_pyr_stream16_kernel<16><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 		else if (o <= 20) lk_pyr_stream16_kernel<20><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 		else lk_pyr_stream16_kernel<24><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);

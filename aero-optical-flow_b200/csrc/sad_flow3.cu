@@ -33,6 +33,9 @@ constexpr int S = 4, NI = 9, W = 64, H = 64, NB = 5, LO = 5, STEP = 10, NBLK = 2
 constexpr int ROWS = 8 + 2 * S;                 // 16 window rows per search column
 constexpr int GAP = 64;                         // bytes inserted after rows 9, 19, ...
 constexpr int SLOT_BYTES = H * W + (H / 10) * GAP + 64;
+// words per aligned reference block in shared memory: 16 used, pitch 20 (80 B, still 16-byte aligned) so that the
+// 128-bit loads of the 8 blocks of a round fall into 8 different groups of 4 banks (pitch 16: two groups, 4-way conflicts)
+constexpr int APITCH = 20;
 
 __host__ __device__ constexpr uint32_t row_off(int y) { return (uint32_t)(y * W + (y / 10) * GAP); }
 // window row r of any block: y = 1 + 10 by + r, so the gap count is by + (r >= 9): static in r up to a per-lane base
@@ -73,6 +76,16 @@ __device__ __forceinline__ uint32_t key9(const uint32_t (&acc)[NI])
 }
 } // namespace
 
+// measured on B200 (gpurun r2e, 4096 / 32768 pairs per launch): rounds unrolled + FMA-pipe alignment 27.1 / 175.0 us,
+// one copy of the round 27.2 / 168.6, funnel shifts only 27.1 / 164.7, both 26.8 / 162.5 -- the kernel is bound by issue
+// slots and instruction fetch (ncu: no_instruction 14 % of the stall samples with the rounds unrolled), not by the ALU
+// pipe alone, so the two extra FMA-pipe instructions per aligned word cost more than the ALU slot they free
+#ifndef AOF_SAD3_UNROLLK
+#define AOF_SAD3_UNROLLK 0
+#endif
+#ifndef AOF_SAD3_FMA
+#define AOF_SAD3_FMA 0
+#endif
 #ifndef AOF_SAD3_MINB
 #define AOF_SAD3_MINB 28 // resident warps per SM the register allocation is capped for
 #endif
@@ -82,7 +95,7 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 		 uint32_t half_mul /* 0x80000000, see havg4_3 */)
 {
 	__shared__ __align__(128) uint8_t s_frame[SLOT_BYTES];
-	__shared__ __align__(16) uint32_t s_ablk[NBLK][16]; // aligned 8x8 blocks of prev
+	__shared__ __align__(16) uint32_t s_ablk[NBLK][APITCH]; // aligned 8x8 blocks of prev
 	__shared__ uint32_t s_key[NBLK];                    // min over candidates of sad << 9 | candidate
 	__shared__ uint32_t s_tex[NBLK];
 	__shared__ int s_vote[NBLK][2];                     // 2*dx + half, 2*dy + half (or INT_MIN)
@@ -109,12 +122,12 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 		pw[k] = sc + row_off(1 + STEP * by) + (o & ~3u);
 		psh[k] = (o & 3u) * 8;
 		pm[k] = 1u << (24 - 8 * (o & 3u));
-		pa[k] = sa + b * 64;
+		pa[k] = sa + b * (APITCH * 4);
 	}
 	// single round: lanes 0..24 = (block lane, dx index 8), lanes 25..31 = (block 24, dx index lane - 25)
 	const int sb = lane < NBLK ? lane : NBLK - 1, sdx = lane < NBLK ? 8 : lane - NBLK;
 	const uint32_t so = (uint32_t)(1 + STEP * (sb % NB) + sdx);
-	const uint32_t sw = sc + row_off(1 + STEP * (sb / NB)) + (so & ~3u), ssh = (so & 3u) * 8, saddr = sa + sb * 64;
+	const uint32_t sw = sc + row_off(1 + STEP * (sb / NB)) + (so & ~3u), ssh = (so & 3u) * 8, saddr = sa + sb * (APITCH * 4);
 	// leftover: (block 24, dx index 7) split by dy over lanes 0..8
 	const uint32_t lo_o = (uint32_t)(1 + STEP * 4 + 7);
 	const uint32_t lw = sc + row_off(1 + STEP * 4 + min(lane, 8)) + (lo_o & ~3u), lsh = (lo_o & 3u) * 8;
@@ -170,9 +183,21 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 
 		// ---- phase B: integer search ----
 		// (the texture gate is applied in phase C only: skipping here would need every lane of a round to agree)
+#if AOF_SAD3_UNROLLK
 #pragma unroll
+#else
+#pragma unroll 1
+#endif
 		for (int k = 0; k < 3; k++) {
+#if AOF_SAD3_UNROLLK
 			const uint32_t wb = pw[k], sh8 = psh[k], m = pm[k], ab = pa[k];
+#else
+			// one copy of the round's code (instruction-cache footprint): the constants are selected, not indexed
+			const uint32_t wb = k == 0 ? pw[0] : k == 1 ? pw[1] : pw[2];
+			const uint32_t sh8 = k == 0 ? psh[0] : k == 1 ? psh[1] : psh[2];
+			const uint32_t m = k == 0 ? pm[0] : k == 1 ? pm[1] : pm[2];
+			const uint32_t ab = k == 0 ? pa[0] : k == 1 ? pa[1] : pa[2];
+#endif
 			uint32_t a[16];
 #pragma unroll
 			for (int j = 0; j < 4; j++)
@@ -186,7 +211,12 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 			for (int r = 0; r < ROWS; r++) {
 				const uint32_t w0 = lds32(wb + wrow(r)), w1 = lds32(wb + wrow(r) + 4), w2 = lds32(wb + wrow(r) + 8);
 				const uint32_t e0 = __funnelshift_r(w0, w1, sh8), e1 = __funnelshift_r(w1, w2, sh8);
+#if AOF_SAD3_FMA
 				const uint32_t o0 = align_fma(w0, w1, m), o1 = align_fma(w1, w2, m);
+#else
+				const uint32_t o0 = __funnelshift_rc(w0, w1, sh8 + 8), o1 = __funnelshift_rc(w1, w2, sh8 + 8);
+				(void)m;
+#endif
 #pragma unroll
 				for (int q = 0; q < NI; q++) {
 					const int br = r - q; // row of the reference block this window row meets at dy = q - S
@@ -235,7 +265,7 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 			uint32_t lkey = 0xFFFFFFFFu;
 			if (lane < NI) {
 				uint32_t acc1 = 0;
-				const uint32_t ab = sa + (NBLK - 1) * 64;
+				const uint32_t ab = sa + (NBLK - 1) * (APITCH * 4);
 #pragma unroll
 				for (int br = 0; br < 8; br++) {
 					const uint32_t ad = lw + br * W + (br + lane >= 9 ? GAP : 0);

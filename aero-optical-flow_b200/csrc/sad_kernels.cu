@@ -457,7 +457,7 @@ template <int S> static cudaError_t launch_sad(const uint8_t *prev, const uint8_
 		if (e != cudaSuccess) return e;
 		attr_set[dev] = true;
 	}
-	KernelTimer kt(KID_SAD_FLOW, st);
+	KernelTimer kt(KID_SAD_FLOW, st, S == 4 ? "sad_flow_kernel<4>" : S == 6 ? "sad_flow_kernel<6>" : "sad_flow_kernel<8>");
 	sad_flow_kernel<S><<<n, SadCfg<S>::THREADS, dyn, st>>>(prev, cur, g, raw, blocks);
 	count_launch();
 	return cudaGetLastError();
@@ -475,7 +475,7 @@ static cudaError_t launch_sad_any(int search, const uint8_t *prev, const uint8_t
 		if (e != cudaSuccess) return e;
 		attr_set[dev] = true;
 	}
-	KernelTimer kt(KID_SAD_FLOW, st);
+	KernelTimer kt(KID_SAD_FLOW, st, "sad_flow_any_kernel");
 	sad_flow_any_kernel<<<n, 256, dyn, st>>>(prev, cur, g, search, raw, blocks);
 	count_launch();
 	return cudaGetLastError();
@@ -486,13 +486,13 @@ cudaError_t sad_flow_launch(int search, const uint8_t *prev, const uint8_t *cur,
 {
 	if (n <= 0) return cudaSuccess;
 	if (sad_flow3_supported(search, g)) {
-		KernelTimer kt(KID_SAD_FLOW, st);
+		KernelTimer kt(KID_SAD_FLOW, st, "sad_flow3_kernel");
 		count_launch();
 		return sad_flow3_launch(prev, cur, g, n, raw, blocks, st);
 	}
 	if (search != 4 && search != 6 && search != 8) return launch_sad_any(search, prev, cur, g, n, raw, blocks, st);
 	if (sad_flow2_supported(g)) {
-		KernelTimer kt(KID_SAD_FLOW, st);
+		KernelTimer kt(KID_SAD_FLOW, st, search == 4 ? "sad_flow2_kernel<4>" : search == 6 ? "sad_flow2_kernel<6>" : "sad_flow2_kernel<8>");
 		count_launch();
 		return sad_flow2_launch(search, prev, cur, g, n, raw, blocks, st);
 	}

@@ -29,8 +29,9 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as entry  # noqa: E402
 
 FX, FY = 216.6677, 216.2457
-# ---- SAD workload
+# ---- SAD workload (config 5 = 65 536 streams over 8 GPUs = 8192 per GPU)
 SAD_STREAMS, SAD_W, SAD_H, SAD_SEARCH, SAD_ROT = int(os.environ.get("AOF_BENCH_SAD_STREAMS", "4096")), 64, 64, 4, 16
+SAD_STREAMS_CONFIG5 = 8192
 SAD_BYTES_PER_PAIR = 2 * SAD_W * SAD_H + 16      # both frames read + 16 B result
 SAD_INSTR_PER_PAIR = 40550                       # packed-byte instructions of the reference algorithm
 # ---- LK workload (SURVEY.md 8(d), config 2 batched)
@@ -41,6 +42,15 @@ LK_BYTES_PER_PAIR = LK_LEVEL_PX[0] + sum(LK_LEVEL_PX[1:])   # new frame read onc
 # ALU pipe at 63 lanes/clk/SM (profiles/r1h_ubench_int_pipes.jsonl; the 125 of the earlier r1g file was ptxas fusing a chain
 # of max into VIMNMX3)
 LK_FAST_OPS_PER_PIXEL_PAIR = 72
+MIN_TIMED_S = 0.5          # the K timed steps are repeated (each repeat bracketed like the first) until this much is timed
+
+
+def workload_name(kind, n):
+    """config.workload: ONE string per workload, the same in the b200 arm and in --impl reference"""
+    if kind == "sad":
+        return "sad64_search4_batch%d (BASELINE config 3: OpticalFlowPX4::calcFlow, %d 64x64 streams per GPU per step)" % (n, n)
+    return ("lk640x480_features20_batch%d (BASELINE config 2 batched as in config 5: OpticalFlowOpenCV::calcFlow, "
+            "%d 640x480 streams per GPU per step, FAST + binned selection + 3-level pyramidal LK 9x9)" % (n, n))
 
 
 def ncu_traffic(kernel, n, n_ref):
@@ -70,49 +80,68 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+    """nvidia-smi clocks / throttle reasons, sampled every 20 ms with nvidia-smi's own timestamps; stop(t0, t1) keeps the
+    samples that fall inside [t0, t1] (the timed region, time.time() seconds)."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
 
-    def start(self):
+    def start(self, wait_s=4.0):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, bufsize=1)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
+            t_end = time.time() + wait_s                      # nvidia-smi needs a moment before its first sample
+            while not self.rows and time.time() < t_end:
+                time.sleep(0.02)
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.time(), line.strip()))
 
-    def stop(self):
+    @staticmethod
+    def _stamp(text, fallback):
+        import datetime
+        try:
+            return datetime.datetime.strptime(text.strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+        except Exception:
+            return fallback
+
+    def stop(self, t0=None, t1=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        sm, mx, reasons, sm_all = [], [], set(), []
+        for t_read, r in self.rows:
             f = [x.strip() for x in r.split(",")]
-            if len(f) < 6:
+            if len(f) < 7:
                 continue
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
+                clk, cmax = float(f[1]), float(f[2])
             except ValueError:
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+            sm_all.append(clk)
+            t = self._stamp(f[0], t_read)
+            if t0 is not None and not (t0 - 0.01 <= t <= t1 + 0.01):
+                continue
+            sm.append(clk); mx.append(cmax)
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "samples_outside_timed_region": len(sm_all) - len(sm),
+                "window": "samples whose nvidia-smi timestamp lies inside the timed region"}
 
 
 def dist_setup():
@@ -147,19 +176,27 @@ def max_over_ranks(ms, world):
     return float(t.item())
 
 
-def time_steps(step, first, steps, world):
-    """`steps` calls of step(k) between a barrier + sync on both sides; device time, max over ranks (ms)."""
+def time_steps(step, first, steps, world, min_s=MIN_TIMED_S, max_repeats=400):
+    """K = `steps` calls of step(k) between a barrier + torch.cuda.synchronize() on both sides, device time from CUDA
+    events on the launching stream, max over ranks.  The K-step region is repeated, every repeat bracketed in the same
+    way, until at least min_s of device time has been timed (a 10 ms region is too short for a clock sampler).
+    -> {"ms": mean ms per K steps, "repeats": R, "all_ms": [...], "t0", "t1": wall-clock bounds, "next": next k}"""
     import torch
-    barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for k in range(steps):
-        step(first + k)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    all_ms, k, repeats = [], first, 1
+    t0 = time.time()
+    while len(all_ms) < repeats:
+        barrier(world)
+        e0.record()
+        for _ in range(steps):
+            step(k); k += 1
+        e1.record()
+        torch.cuda.synchronize()
+        all_ms.append(max_over_ranks(e0.elapsed_time(e1), world))       # the same number on every rank
+        if len(all_ms) == 1:
+            repeats = int(min(max_repeats, max(1, np.ceil(min_s * 1e3 / max(all_ms[0], 1e-3)))))
     barrier(world)
-    return ms
+    return {"ms": float(np.mean(all_ms)), "repeats": repeats, "all_ms": all_ms, "t0": t0, "t1": time.time(), "next": k}
 
 
 # ----------------------------------------------------------------------------- synthetic inputs

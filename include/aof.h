@@ -167,6 +167,11 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 void aof_lk_destroy(aof_lk *h);
 int aof_lk_num_streams(const aof_lk *h);
 int aof_lk_num_features(const aof_lk *h);
+/* diagnostics of the lazy FAST path since create / reset (synchronises the device): out[0] = bins whose picks were found
+ * without scoring every pixel, out[1] = candidate-pool rebuilds, out[2] = bins that overflowed the lazy buffers,
+ * out[3] = stream-frames handed to the complete path (second-chance pass of initMorePoints).  All zero when the
+ * shape or AOF_FAST_LAZY=0 selects the complete path. */
+int aof_lk_lazy_stats(aof_lk *h, uint64_t out[4]);
 int aof_lk_reset(aof_lk *h);
 
 /* replaces OpticalFlowOpenCV::calcFlow (src/flow_opencv.cpp:89-210), 1-stream

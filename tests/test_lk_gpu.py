@@ -259,3 +259,65 @@ def test_large_frames_match_oracle(pkg, w, h, nf):
             assert (raw["inliers"][i], raw["fast_bins"][i], raw["active"][i]) == (os_["inliers"], os_["fast_bins"], os_["active"])
             check_state(gs, i, os_)
     f.close()
+
+
+def _run_sequences(pkg, frames, w, h, nf, rate=-1):
+    n, T = frames.shape[1], frames.shape[0]
+    f = pkg.LkFlow(FX, FY, rate, w, h, nf, n_streams=n)
+    outs = []
+    for k in range(T):
+        res, raw = f.calc_flow_batch(frames[k], np.full(n, 1000 + 13333 * k, np.uint32), want_raw=True)
+        outs.append((res.copy(), raw.copy(), {key: v.copy() for key, v in f.state().items()}))
+    stats = f.lazy_stats()
+    f.close()
+    return outs, stats
+
+
+@pytest.mark.parametrize("w,h,nf", [(640, 480, 20), (320, 240, 50), (128, 128, 20), (256, 192, 100)])
+def test_lazy_fast_equals_complete_path(pkg, w, h, nf, monkeypatch):
+    """lk_fast_pick_kernel (lazy FAST: bound, pool, exact scores of the candidates only) against the complete keypoint
+    lists (AOF_FAST_LAZY=0), byte for byte: outputs, diagnostics and the whole tracker state, frame by frame; includes
+    a scene cut (every feature lost: all 16 bins requested again) and flat frames (no corner anywhere)."""
+    n, T = 12, 9
+    rng = np.random.default_rng(w + nf)
+    seqs = [pkg.synth.lk_sequence(T, w, h, int(rng.integers(-4, 5)), int(rng.integers(-4, 5)), seed=900 + i,
+                                  sigma=float(rng.choice([1.2, 2.0, 3.5]))) for i in range(n)]
+    frames = np.stack([np.stack([seqs[i][k] for i in range(n)]) for k in range(T)])
+    frames[5, :4] = frames[0, 4:8]                       # scene cut for four streams
+    frames[6, 8] = 90                                    # a flat frame
+    frames[:, 9] = (frames[:, 9] // 8) + 100             # a low-contrast stream: bounds below any learnt floor
+    monkeypatch.setenv("AOF_FAST_LAZY", "1")
+    lazy, stats = _run_sequences(pkg, frames, w, h, nf)
+    monkeypatch.setenv("AOF_FAST_LAZY", "0")
+    full, stats0 = _run_sequences(pkg, frames, w, h, nf)
+    assert stats0 == (0, 0, 0, 0) and stats[0] > 0, (stats, stats0)
+    for k in range(T):
+        assert lazy[k][0].tobytes() == full[k][0].tobytes(), k
+        assert lazy[k][1].tobytes() == full[k][1].tobytes(), k
+        for key in full[k][2]:
+            assert np.array_equal(lazy[k][2][key], full[k][2][key]), (k, key)
+    # and against the oracle for two of the streams
+    for i in (0, 9):
+        o = olk.Tracker(FX, FY, -1, w, h, nf)
+        for k in range(T):
+            q, dt, fx, fy = o.calc_flow(frames[k, i], 1000 + 13333 * k)
+            r = lazy[k][0]
+            assert (r["quality"][i], r["flow_x"][i], r["flow_y"][i]) == (q, np.float32(fx), np.float32(fy)), (i, k)
+
+
+def test_lazy_fast_second_chance_goes_through_the_complete_path(pkg):
+    """sparse blobs: fewer acceptable keypoints than requests, so initMorePoints' second-chance pass runs
+    (trackFeatures.cpp:266-304); the lazy selection must hand those streams to the complete path and still equal the oracle"""
+    from test_ref_lk import blob_sequence
+    w, h, nf, T = 320, 240, 33, 6
+    seqs = [blob_sequence(T, w, h, 2, -1, 41 + i) for i in range(4)]
+    frames = np.stack([np.stack([seqs[i][k] for i in range(4)]) for k in range(T)])
+    got, stats = _run_sequences(pkg, frames, w, h, nf)
+    assert stats[3] > 0, stats                           # the fallback really ran
+    for i in range(4):
+        o = olk.Tracker(FX, FY, -1, w, h, nf)
+        for k in range(T):
+            q, dt, fx, fy = o.calc_flow(frames[k, i], 1000 + 13333 * k)
+            r = got[k][0]
+            assert (r["quality"][i], r["flow_x"][i], r["flow_y"][i]) == (q, np.float32(fx), np.float32(fy)), (i, k)
+            check_state(got[k][2], i, o.state())

@@ -1,8 +1,9 @@
 #!/bin/bash
-# tuning aid: run the SAD bench once per prebuilt library variant in tmp_variants/ at 4096 and 32768 pairs per launch
+# tuning aid: parity + SAD bench once per prebuilt library variant in tmp_variants/ at 4096 and 32768 pairs per launch
 cp aero-optical-flow_b200/libaof_b200.so /tmp/keep.so
 for f in tmp_variants/lib_*.so; do
   cp $f aero-optical-flow_b200/libaof_b200.so
+  python -m pytest tests/test_sad_gpu.py -x -q -k "golden or kat or batch" 2>&1 | tail -1
   for n in 4096 32768; do
   AOF_BENCH_SAD_STREAMS=$n python bench.py --no-cpu --steps 300 --warmup 3 --workload sad 2>>gpurun_out/variants.err | python -c "
 import json,sys
