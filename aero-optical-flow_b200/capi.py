@@ -177,7 +177,7 @@ class Px4Flow:
         check(L.aof_px4_create(C.byref(self.params), n_streams, device, C.byref(self.handle)), "aof_px4_create")
 
     def close(self):
-        if getattr(self, "handle", None):
+        if getattr(self, "handle", None) and lib is not None:   # (module globals are gone at interpreter exit)
             lib().aof_px4_destroy(self.handle)
             self.handle = None
 
@@ -238,7 +238,7 @@ class LkFlow:
         check(L.aof_lk_create(C.byref(self.params), n_streams, device, C.byref(self.handle)), "aof_lk_create")
 
     def close(self):
-        if getattr(self, "handle", None):
+        if getattr(self, "handle", None) and lib is not None:   # (module globals are gone at interpreter exit)
             lib().aof_lk_destroy(self.handle)
             self.handle = None
 
@@ -336,7 +336,7 @@ class _Multi:
         return devices, (C.c_int * len(devices))(*devices)
 
     def close(self):
-        if getattr(self, "handle", None):
+        if getattr(self, "handle", None) and lib is not None:   # (module globals are gone at interpreter exit)
             getattr(lib(), "aof_%s_destroy_multi" % self._kind)(self.handle)
             self.handle = None
 
@@ -438,7 +438,7 @@ class SadDense:
         self.nbx, self.nby, self.x0, self.y0 = [x.value for x in g]
 
     def close(self):
-        if getattr(self, "handle", None):
+        if getattr(self, "handle", None) and lib is not None:   # (module globals are gone at interpreter exit)
             lib().aof_sad_dense_destroy(self.handle)
             self.handle = None
 
@@ -466,7 +466,7 @@ class Gftt:
         check(lib().aof_gftt_create(width, height, device, C.byref(self.handle)), "aof_gftt_create")
 
     def close(self):
-        if getattr(self, "handle", None):
+        if getattr(self, "handle", None) and lib is not None:   # (module globals are gone at interpreter exit)
             lib().aof_gftt_destroy(self.handle)
             self.handle = None
 

@@ -155,7 +155,27 @@ def dist_setup():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if not dist.is_initialized():
             dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        global HOST_GROUP
+        HOST_GROUP = dist.new_group(backend="gloo")          # the host-side gather of the results (no data-path collective)
     return rank, world, local
+
+
+HOST_GROUP = None
+
+
+def host_gather(res, rank, world):
+    """rank 0 receives every rank's result records (16 B per stream) over the host group: the 'host gather' of SURVEY.md
+    8(e).  -> on rank 0 the concatenated records of all ranks, elsewhere None"""
+    if world == 1:
+        return res
+    import torch
+    import torch.distributed as dist
+    t = torch.from_numpy(np.ascontiguousarray(res).view(np.uint8).reshape(-1))
+    out = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    dist.gather(t, out, dst=0, group=HOST_GROUP)
+    if rank != 0:
+        return None
+    return np.concatenate([o.numpy() for o in out]).view(res.dtype)
 
 
 def barrier(world):
@@ -266,64 +286,171 @@ def cpu_sad(frames, budget_s):
             "sample": "%d x %d SAD 64x64 +-%d pairs, PX4Flow::compute_flow (%s), %d host threads" % (reps, n, SAD_SEARCH, kind, threads)}
 
 
-def cpu_lk(frames, budget_s):
-    """oracle/lk_oracle.c trackers (flow_opencv.cpp cannot be compiled here: kind 'port'), one per stream,
-    spread over all host cores with threads (ctypes releases the GIL inside the C call)."""
+def _lk_cpu_tracker_factory():
+    """-> (make(), kind, what): the reference's own OpticalFlowOpenCV object where it can run --
+    oracle/_ref/libaof_ref_lk.so = trackFeatures.cpp + flow_opencv.cpp + optical_flow.cpp compiled unmodified, calling
+    the real OpenCV (cv2: FAST, calcOpticalFlowPyrLK) the way the reference links it -- else the same objects over
+    oracle/lk_oracle.c's restatement of those three OpenCV calls, else the C port alone."""
+    from oracle import ref_lk
+    if ref_lk.available():
+        try:
+            import cv2  # noqa: F401
+            return (lambda: ref_lk.RefTracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES, backend="cv2")), "reference", \
+                "the reference's trackFeatures.cpp + flow_opencv.cpp objects (oracle/_ref) over OpenCV %s via cv2, 1 OpenCV thread per process" % cv2.__version__
+        except Exception:
+            return (lambda: ref_lk.RefTracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES)), "port", \
+                "the reference's trackFeatures.cpp + flow_opencv.cpp objects (oracle/_ref) over oracle/lk_oracle.c's FAST / PyrLK"
     from oracle import lk as olk
-    cores = os.cpu_count() or 1
-    rot, n = frames.shape[:2]
-    tr = olk.Tracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES)
-    tr.calc_flow(frames[0, 0], 0)
-    t0 = time.perf_counter(); tr.calc_flow(frames[1, 0], 1000); per_pair = time.perf_counter() - t0
-    n_frames = 4                                             # calls per stream after the priming frame
-    streams = int(max(cores, min(n, budget_s * cores / (per_pair * n_frames))))
-    trackers = [olk.Tracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES) for _ in range(streams)]
-    for i, t in enumerate(trackers):
-        t.calc_flow(frames[0, i % n], 0)                     # priming frame (detection only), untimed
+    return (lambda: olk.Tracker(FX, FY, -1, LK_W, LK_H, LK_FEATURES)), "port", "oracle/lk_oracle.c (CPU restatement of the whole path)"
 
-    def work(tid):
-        for i in range(tid, streams, cores):
-            for k in range(1, n_frames + 1):
-                trackers[i].calc_flow(frames[k % rot, i % n], 1000 * k)
 
-    th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
-    t0 = time.perf_counter()
-    for t in th:
-        t.start()
-    for t in th:
-        t.join()
-    dt = time.perf_counter() - t0
-    return {"value": streams * n_frames / dt, "unit": "frame-pairs/s", "cores": cores, "kind": "port",
-            "sample": "%d streams x %d frames, LK 640x480, 20 features, oracle/lk_oracle.c (CPU restatement of "
-                      "flow_opencv.cpp + trackFeatures.cpp + the OpenCV arithmetic), %d host threads" % (streams, n_frames, cores)}
+def _lk_cpu_worker(wid, procs, path, shape, conn):
+    """one process = the trackers of streams wid, wid + procs, ...; a step = calcFlow of ONE frame on each of them"""
+    try:
+        devnull = os.open(os.devnull, os.O_WRONLY)           # the reference prints from calcFlow: keep bench's stdout to its ONE line
+        os.dup2(devnull, 1)
+        make, _, _ = _lk_cpu_tracker_factory()
+        frames = np.memmap(path, dtype=np.uint8, mode="r", shape=shape)
+        rot, n = frames.shape[:2]
+        mine = list(range(wid, n, procs))
+        trackers = [make() for _ in mine]
+        for t, i in zip(trackers, mine):
+            t.calc_flow(frames[0, i], 0)                     # priming frame (detection only), untimed
+        conn.send(("ready", len(mine)))
+        while True:
+            k = conn.recv()
+            if k is None:
+                break
+            q_ok = 0
+            for t, i in zip(trackers, mine):
+                q = t.calc_flow(frames[k % rot, i], 1000 * k)[0]
+                q_ok += q > 60
+            conn.send(("done", q_ok))
+    except Exception as e:                                   # noqa: BLE001
+        conn.send(("error", repr(e)))
+
+
+class CpuLk:
+    """The LK workload on the host cores: one process per core (the reference's tracker keeps its state in file statics,
+    and the cv2 callbacks hold the GIL, so threads would serialise), whole streams per process, a step = one calcFlow
+    pass over all n streams -- the same step as the GPU arm's."""
+
+    def __init__(self, frames, procs=None):
+        import multiprocessing as mp
+        import tempfile
+        self.n = frames.shape[1]
+        self.procs = min(procs or (os.cpu_count() or 1), self.n)
+        _, self.kind, self.what = _lk_cpu_tracker_factory()
+        # the frames go through a file in shared memory: workers are SPAWNED (a fork of a process that holds a CUDA
+        # context and its threads is not safe), and page-locked memory does not survive a fork anyway
+        shm = "/dev/shm" if os.path.isdir("/dev/shm") else None
+        fd, self.path = tempfile.mkstemp(prefix="aof_bench_lk_", suffix=".u8", dir=shm)
+        os.close(fd)
+        mm = np.memmap(self.path, dtype=np.uint8, mode="w+", shape=frames.shape)
+        mm[:] = frames
+        mm.flush()
+        del mm
+        ctx = mp.get_context("spawn")
+        self.workers = []
+        for w in range(self.procs):
+            a, b = ctx.Pipe()
+            pr = ctx.Process(target=_lk_cpu_worker, args=(w, self.procs, self.path, tuple(frames.shape), b), daemon=True)
+            pr.start()
+            self.workers.append((pr, a))
+        for _, c in self.workers:
+            tag, v = c.recv()
+            if tag != "ready":
+                raise RuntimeError("cpu LK worker: %s" % (v,))
+        self.k = 1
+
+    def step(self):
+        """-> seconds of wall clock for one pass over the n streams"""
+        t0 = time.perf_counter()
+        for _, c in self.workers:
+            c.send(self.k)
+        ok = 0
+        for _, c in self.workers:
+            tag, v = c.recv()
+            if tag != "done":
+                raise RuntimeError("cpu LK worker: %s" % (v,))
+            ok += v
+        dt = time.perf_counter() - t0
+        self.k += 1
+        assert ok > 0.9 * self.n, "CPU LK arm lost track (%d of %d streams with quality > 60)" % (ok, self.n)
+        return dt
+
+    def close(self):
+        for pr, c in self.workers:
+            try:
+                c.send(None)
+            except Exception:
+                pass
+        for pr, _ in self.workers:
+            pr.join(timeout=5)
+            if pr.is_alive():
+                pr.terminate()
+        try:
+            os.unlink(self.path)
+        except OSError:
+            pass
+
+
+def cpu_lk(frames, budget_s):
+    """cpu_baseline of the LK workload: a bounded sample (whole passes over the batch until budget_s is spent, at least 2)"""
+    arm = CpuLk(frames)
+    try:
+        times = [arm.step()]
+        while sum(times) < budget_s and len(times) < 50 or len(times) < 2:
+            times.append(arm.step())
+    finally:
+        arm.close()
+    med = float(np.median(times))
+    return {"value": arm.n / med, "unit": "frame-pairs/s", "cores": arm.procs, "kind": arm.kind,
+            "sample": "%d passes over %d streams (640x480, 20 features), median pass %.3f s; %s; %d processes" %
+                      (len(times), arm.n, med, arm.what, arm.procs)}
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only), on the b200 arm's
+    own workload: a step = one calcFlow pass over the same batch of streams."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     entry.build_oracles()
-    budget = 60.0
-    if args.workload == "sad":
-        frames, _ = sad_host_frames(SAD_STREAMS, 3, 1)
-        workload, fn = "sad64_batch4096_search4", cpu_sad
-    else:
-        frames, _ = lk_host_frames(64, LK_ROT, 1)
-        workload, fn = "lk640x480_features20", cpu_lk
     total = max(1, args.steps + args.warmup)
-    vals = []
-    for k in range(total):
-        r = fn(frames, budget / total)
-        if k >= args.warmup:
-            vals.append(r)
-    v = float(np.mean([r["value"] for r in vals]))
-    ms = 1e3 * float(np.mean([1.0 / r["value"] for r in vals]))
-    cb = dict(vals[-1]); cb["value"] = v
+    if args.workload == "sad":
+        n = SAD_STREAMS
+        frames, _ = sad_host_frames(n, 3, 1)
+        fn, kind = cpu_sad_runner()
+        cores = os.cpu_count() or 1
+        threads = cores if kind == "reference" else 1
+        times = []
+        for k in range(total):
+            t0 = time.perf_counter(); fn(frames[k % 2], frames[k % 2 + 1], threads); times.append(time.perf_counter() - t0)
+        times = times[args.warmup:]
+        what = "PX4Flow::compute_flow of the reference (oracle/_ref), %d host threads" % threads if kind == "reference" else \
+            "oracle/sad_oracle.c (CPU restatement), 1 thread"
+        workload = workload_name("sad", n)
+    else:
+        n = args.lk_streams
+        frames, _ = lk_host_frames(n, LK_ROT, 2000)
+        arm = CpuLk(frames)
+        try:
+            times = [arm.step() for _ in range(total)][args.warmup:]
+        finally:
+            arm.close()
+        kind, threads, what = arm.kind, arm.procs, arm.what
+        workload = workload_name("lk", n)
+    ms = 1e3 * float(np.mean(times))
+    v = n / (ms * 1e-3)
+    cb = {"value": v, "unit": "frame-pairs/s", "cores": threads, "kind": kind,
+          "sample": "%d steps of %d streams each (%d stream-frames), mean step %.1f ms; %s" % (len(times), n, len(times) * n, ms, what)}
     print(json.dumps({
         "impl": "reference", "metric": "frame-pairs/s", "value": v, "unit": "frame-pairs/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload, "note": "each step is a bounded sample of the workload on the host cores; ms_per_step is per frame pair"},
+        "config": {"workload": workload, "streams_per_step": n,
+                   "note": "host cores only (the reference has no GPU path): one step = one calcFlow pass over the batch; "
+                           "the value does not grow with --gpus"},
         "cpu_baseline": cb, "e2e": {"value": v, "unit": "frame-pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
@@ -348,11 +475,54 @@ def pinned_frames(shape):
     return t, t.numpy()
 
 
-def run_sad_gpu(args, rank, world, local, with_cpu):
+def h2d_probe(keep, world):
+    """Pinned host -> device bandwidth of this box as the end-to-end path sees it: one cudaMemcpyAsync of up to 256 MiB of the
+    bench's own pinned frames, all ranks at the same time (they share the host side), best of 5, GB/s of THIS rank -> the
+    min over ranks (the slowest link bounds the max-over-ranks e2e time)."""
+    import torch
+    src = keep.reshape(-1)[: 256 << 20]
+    dst = torch.empty_like(src, device="cuda")
+    best = 0.0
+    for _ in range(5):
+        barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); dst.copy_(src, non_blocking=True); e1.record()
+        torch.cuda.synchronize()
+        best = max(best, src.numel() / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+    del dst
+    return -max_over_ranks(-best, world)
+
+
+def time_e2e(call, first, steps, world, min_s=MIN_TIMED_S):
+    """host-API steps (synchronous calls: H2D, kernels, D2H inside) between barriers, wall clock, max over ranks; the
+    step count is raised until min_s is timed.  -> (ms total, steps timed, last result)"""
+    import torch
+    barrier(world)
+    t0 = time.perf_counter(); res = call(first); probe = time.perf_counter() - t0
+    probe = max_over_ranks(probe * 1e3, world) * 1e-3
+    steps = int(max(steps, min(2000, np.ceil(min_s / max(probe, 1e-6)))))
+    barrier(world)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        res = call(first + 1 + k)
+    torch.cuda.synchronize()
+    return max_over_ranks((time.perf_counter() - t0) * 1e3, world), steps, res
+
+
+def find_kernel(kb, prefix):
+    """the entry of the timing table whose kernel symbol starts with `prefix` (the table names what actually ran)"""
+    for name in kb:
+        if name.startswith(prefix):
+            return name
+    raise KeyError("no kernel %s* in %s" % (prefix, sorted(kb)))
+
+
+def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False):
+    """light: the throughput legs only (timed region + end to end), for the extra config-5 size"""
     import torch
     pkg = entry.load_package()
     L = pkg.lib()
-    n, rot = SAD_STREAMS, SAD_ROT
+    n, rot = n_streams or SAD_STREAMS, SAD_ROT
     frames, vel = sad_host_frames(n, rot, seed=1000 + rank)
     keep, h_frames = pinned_frames(frames.shape)
     h_frames[:] = frames
@@ -369,21 +539,16 @@ def run_sad_gpu(args, rank, world, local, with_cpu):
     def step(k):
         flow.calc_flow_device(fptr[k % rot], tptr[k % rot], d_out.data_ptr(), stream=stream)
 
-    for k in range(args.warmup + 1):          # +1: the priming frame launches nothing
-        step(k)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for k in range(args.warmup + 1):          # +1: the priming frame launches nothing
+        step(k)
     l0 = L.aof_launch_count()
-    ms = time_steps(step, args.warmup + 1, args.steps, world)
-    launches = L.aof_launch_count() - l0
-    t_end = time.time() + max(0.0, 1.5 - ms * 1e-3)   # keep the same loop running until the sampler has >= 1.5 s of it
-    k = 0
-    while time.time() < t_end:
-        for _ in range(200):
-            step(k); k += 1
-        torch.cuda.synchronize()
-    clocks = sampler.stop() if rank == 0 else None
+    tm = time_steps(step, args.warmup + 1, args.steps, world)
+    launches = (L.aof_launch_count() - l0) // tm["repeats"]
+    ms, k = tm["ms"], tm["next"]
+    clocks = sampler.stop(tm["t0"], tm["t1"]) if rank == 0 else None
     out = d_out.cpu().numpy().view(pkg.capi.flow_out_dtype).reshape(-1)
     assert (out["quality"] == 255).mean() > 0.99, "timed SAD path produced implausible quality"
     kb = kernel_breakdown(pkg, step, k, min(args.steps, 200))
@@ -391,31 +556,30 @@ def run_sad_gpu(args, rank, world, local, with_cpu):
     # end to end through the host API: pinned host frames -> H2D -> kernels -> 16 B/stream D2H
     flow_e = pkg.Px4Flow(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=n, device=local)
     t_us = np.zeros(n, np.uint32)
-    e_steps = max(3, min(args.steps, 200))
     for k in range(4):
         flow_e.calc_flow_batch(h_frames[k % rot], t_us + 1000 * k)
-    barrier(world)
-    t0 = time.perf_counter()
-    for k in range(e_steps):
-        res = flow_e.calc_flow_batch(h_frames[(k + 4) % rot], t_us + 1000 * (k + 4))
-    torch.cuda.synchronize()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
-    assert (res["quality"] == 255).mean() > 0.99
+    e2e_ms, e_steps, res = time_e2e(lambda j: host_gather(flow_e.calc_flow_batch(h_frames[(j + 4) % rot], t_us + 1000 * (j + 4)), rank, world),
+                                    0, min(args.steps, 200), world)
+    if rank == 0:
+        assert res.size == world * n and (res["quality"] == 255).mean() > 0.99
     flow_e.close(); flow.close()
+    h2d_gbs = h2d_probe(keep, world)
 
     # BASELINE config 1 as written: ONE 64x64 stream, host frame in, result out (latency, not throughput)
-    one = pkg.Px4Flow(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=1, device=local)
-    for k in range(4):
-        one.calc_flow(h_frames[k % rot, 0], 1000 * k)
-    t0 = time.perf_counter()
-    for k in range(100):
-        one.calc_flow(h_frames[(k + 4) % rot, 0], 1000 * (k + 4))
-    lat_us = (time.perf_counter() - t0) / 100 * 1e6
-    one.close()
+    lat_us = None
+    if not light:
+        one = pkg.Px4Flow(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=1, device=local)
+        for k in range(4):
+            one.calc_flow(h_frames[k % rot, 0], 1000 * k)
+        t0 = time.perf_counter()
+        for k in range(100):
+            one.calc_flow(h_frames[(k + 4) % rot, 0], 1000 * (k + 4))
+        lat_us = (time.perf_counter() - t0) / 100 * 1e6
+        one.close()
 
     # BASELINE config 4: dense block field of 1280x720 pairs, +-8 (device-resident pairs, 8 distinct pairs rotating)
     dense = None
-    if rank == 0:
+    if rank == 0 and not light:
         dn, dw, dh, ds = 8, 1280, 720, 8
         rng = np.random.default_rng(77)
         tex = pkg.synth.box_blur3(rng.integers(0, 256, (dh + 32, dw + 32), dtype=np.uint8))
@@ -449,40 +613,58 @@ def run_sad_gpu(args, rank, world, local, with_cpu):
         return None
     pk = peaks()
     dom = max(kb, key=lambda kname: kb[kname]["ms_per_step"])
-    kern_ms = kb["sad_flow_kernel"]["ms_per_step"]
-    achieved = n * SAD_BYTES_PER_PAIR / (kern_ms * 1e-3) / 1e9
+    kname = find_kernel(kb, "sad_flow")                       # the SAD kernel that ran (sad_flow3_kernel at 64x64 +-4)
+    kern_ms = kb[kname]["ms_per_step"] / max(1.0, kb[kname]["launches_per_step"])
+    hbm = n * SAD_BYTES_PER_PAIR / (kern_ms * 1e-3) / 1e9
+    hbm_obj = {"bound": "hbm", "achieved": hbm, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm / pk["hbm_gbs"],
+               "peak_source": pk["which"], "algorithmic_bytes_per_launch": n * SAD_BYTES_PER_PAIR,
+               "traffic": ncu_traffic("sad_flow_kernel", n, 4096)}
+    if "alu_packed_instr_per_s" in pk:
+        # the binding roofline: 40 550 packed-byte SAD instructions per pair against the measured
+        # VABSDIFF4 issue rate of the ALU pipe (profiles/alu_peak.json, tools/ubench.cu)
+        a = n * SAD_INSTR_PER_PAIR / (kern_ms * 1e-3)
+        roof = {"bound": "int-alu", "achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
+                "frac": a / pk["alu_packed_instr_per_s"], "peak_source": pk["alu_which"] + " (tools/ubench.cu, VABSDIFF4 issue rate)",
+                "algorithmic_instr_per_pair": SAD_INSTR_PER_PAIR, "algorithmic_instr_per_launch": n * SAD_INSTR_PER_PAIR,
+                "traffic": hbm_obj["traffic"], "hbm": hbm_obj}
+    else:
+        roof = dict(hbm_obj, note="profiles/alu_peak.json missing: the binding integer-ALU roofline cannot be stated")
+    roof.update({"kernel": kname, "kernel_ms": kern_ms, "dominant_kernel_by_time": dom})
+    e2e_v = world * n * e_steps / (e2e_ms * 1e-3)
+    e2e_gbs = (fb + 4 * n) * e_steps / (e2e_ms * 1e-3) / 1e9
     r = {
         "value": world * n * args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
-        "config": {"workload": "sad64_batch4096_search4 (BASELINE config 3: OpticalFlowPX4::calcFlow, 4096 streams/GPU/launch)",
+        "timed_region": {"repeats": tm["repeats"], "steps_per_repeat": args.steps, "total_s": sum(tm["all_ms"]) * 1e-3,
+                         "ms_per_step_min": min(tm["all_ms"]) / args.steps, "ms_per_step_max": max(tm["all_ms"]) / args.steps},
+        "config": {"workload": workload_name("sad", n),
                    "streams_per_gpu": n, "image": "64x64", "search": SAD_SEARCH, "output_rate": -1,
                    "l2": "current frames rotate over %d buffers = %d MiB > 126 MB L2; the previous frame is last step's "
                          "current frame by construction of calcFlow" % (rot, rot * fb >> 20),
                    "parallelism": "streams sharded across ranks, host gather, no collective"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic("sad_flow_kernel", n, 4096),
-                     "peak_source": pk["which"], "kernel": "sad_flow_kernel<4>", "kernel_ms": kern_ms, "dominant_kernel_by_time": dom,
-                     "algorithmic_bytes_per_launch": n * SAD_BYTES_PER_PAIR},
+        "roofline": roof,
         "kernels": kb,
-        "e2e": {"value": world * n * e_steps / (e2e_ms * 1e-3), "unit": "frame-pairs/s",
+        "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": 16 * n, "steps": e_steps,
-                "api": "aof_px4_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)"},
+                "api": "aof_px4_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
+                       (", then every rank's records gathered on rank 0 over the host (gloo) group" if world > 1 else ""),
+                "roofline": {"bound": "pcie-h2d", "achieved": e2e_gbs, "peak": h2d_gbs, "unit": "GB/s per GPU",
+                             "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
+                             "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},
         "gpu_launches": int(launches), "clocks": clocks, "dtype": "u8",
     }
-    if "alu_packed_instr_per_s" in pk:
-        a = n * SAD_INSTR_PER_PAIR / (kern_ms * 1e-3)
-        r["roofline_int_alu"] = {"bound": "int-alu (VABSDIFF4 issue rate, the binding one)", "achieved": a,
-                                 "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
-                                 "frac": a / pk["alu_packed_instr_per_s"], "peak_source": pk["alu_which"],
-                                 "algorithmic_instr_per_pair": SAD_INSTR_PER_PAIR}
     r["single_stream_latency_us"] = lat_us
     if dense is not None:
         if "alu_packed_instr_per_s" in pk:
             a = dense["blocks_per_pair"] * 4944.0 * dense["pairs_per_s"]     # 289 x 16 SAD + 320 sub-pixel instr per block
-            dense["roofline_int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
-                                         "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_block": 4944}
+            dense["roofline"] = {"bound": "int-alu", "achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed-byte instr/s",
+                                 "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_block": 4944,
+                                 "kernel": "sad_dense_kernel<8>"}
         r["dense"] = dense
     if with_cpu:
         r["cpu_baseline"] = cpu_sad(frames, 10.0)
+        r["vs_cpu"] = {"e2e_over_cpu": e2e_v / r["cpu_baseline"]["value"], "device_resident_over_cpu": r["value"] / r["cpu_baseline"]["value"],
+                       "note": "GPU end-to-end (host frames in, results out) over the reference's CPU code on this box's %d host threads; "
+                               "a reported baseline, not a quality measure" % r["cpu_baseline"]["cores"]}
     return r
 
 
@@ -507,21 +689,16 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     def step(k):
         flow.calc_flow_device(fptr[k % rot], tptr[k % rot], d_out.data_ptr(), d_raw.data_ptr(), stream=stream)
 
-    for k in range(args.warmup + 1):          # +1: the first frame only detects
-        step(k)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for k in range(args.warmup + 1):          # +1: the first frame only detects
+        step(k)
     l0 = L.aof_launch_count()
-    ms = time_steps(step, args.warmup + 1, args.steps, world)
-    launches = L.aof_launch_count() - l0
-    k = args.warmup + 1 + args.steps
-    t_end = time.time() + max(0.0, 1.5 - ms * 1e-3)
-    while time.time() < t_end:
-        for _ in range(20):
-            step(k); k += 1
-        torch.cuda.synchronize()
-    clocks = sampler.stop() if rank == 0 else None
+    tm = time_steps(step, args.warmup + 1, args.steps, world)
+    launches = (L.aof_launch_count() - l0) // tm["repeats"]
+    ms, k = tm["ms"], tm["next"]
+    clocks = sampler.stop(tm["t0"], tm["t1"]) if rank == 0 else None
     # parity spot check of the timed path: the flow of a translating texture is its translation
     raw = d_raw.cpu().numpy().view(pkg.capi.lk_raw_dtype).reshape(-1)
     p = (k - 1) % rot
@@ -529,24 +706,23 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     ok = (np.abs(raw["px_x"] - sign * vel[:, 0]) < 1e-2) & (np.abs(raw["px_y"] - sign * vel[:, 1]) < 1e-2) & (raw["inliers"] >= 5)
     assert ok.mean() > 0.97, "timed LK path does not recover the translations (%.3f ok)" % ok.mean()
     bins_frac = float(raw["fast_bins"].mean()) / 16.0   # share of the 16 bins FAST ran on in the last timed step (steady state)
+    lazy0 = flow.lazy_stats()
     kb = kernel_breakdown(pkg, step, k, min(args.steps, 50))
+    lazy1 = flow.lazy_stats()
     k += min(args.steps, 50)
 
     # end to end through the host API: pinned host frames -> H2D -> kernels -> 16 B/stream D2H
     flow.close()
     flow_e = pkg.LkFlow(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=n, device=local)
     t_us = np.zeros(n, np.uint32)
-    e_steps = max(3, min(args.steps, 30))
     for j in range(3):
         flow_e.calc_flow_batch(h_frames[j % rot], t_us + 1000 * j)
-    barrier(world)
-    t0 = time.perf_counter()
-    for j in range(e_steps):
-        res = flow_e.calc_flow_batch(h_frames[(j + 3) % rot], t_us + 1000 * (j + 3))
-    torch.cuda.synchronize()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
-    assert (res["quality"] > 60).mean() > 0.97
+    e2e_ms, e_steps, res = time_e2e(lambda j: host_gather(flow_e.calc_flow_batch(h_frames[(j + 3) % rot], t_us + 1000 * (j + 3)), rank, world),
+                                    0, min(args.steps, 30), world)
+    if rank == 0:
+        assert res.size == world * n and (res["quality"] > 60).mean() > 0.97
     flow_e.close()
+    h2d_gbs = h2d_probe(keep, world)
 
     # single-stream latency (BASELINE config 2 as written: one stream, host frame in, result out)
     one = pkg.LkFlow(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=1, device=local)
@@ -562,58 +738,91 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     pk = peaks()
     dom = max(kb, key=lambda kname: kb[kname]["ms_per_step"])
     step_ms = ms / args.steps
-    # per-kernel rooflines: algorithmic bytes / packed integer operations per launch
+    # per-kernel rooflines.  Keys are prefixes of the kernel symbols the timing table reports.
+    #   bytes: algorithmic HBM bytes per launch;  alu: packed integer instructions per launch
     px0 = LK_LEVEL_PX[0]
-    alg_bytes = {"lk_pyr_down_kernel": n * (px0 + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0,
-                 "lk_pyr_fused_kernel": n * LK_BYTES_PER_PAIR,      # level 0 read once + levels 1..3 written
-                 "lk_fast_kernel": n * px0 * bins_frac}              # level 0 of the bins that need features
-    # FAST response (the arc-pair network) per PAIR of pixels, every pixel of a bin that needs features scored
-    alg_alu = {"lk_fast_kernel": n * (px0 / 2.0) * bins_frac * LK_FAST_OPS_PER_PIXEL_PAIR}
+    lazy = [b1 - b0 for b0, b1 in zip(lazy0, lazy1)]
+    k_steps = min(args.steps, 50)
+    fast_alu = n * (px0 / 2.0) * bins_frac * LK_FAST_OPS_PER_PIXEL_PAIR
+    spec = {
+        "lk_pyr_stream": {"bound": "hbm", "bytes": n * LK_BYTES_PER_PAIR},          # level 0 read once + levels 1..3 written
+        "lk_pyr_fused": {"bound": "hbm", "bytes": n * LK_BYTES_PER_PAIR},
+        "lk_pyr_down": {"bound": "hbm", "bytes": n * (px0 + 2 * sum(LK_LEVEL_PX[1:3]) + sum(LK_LEVEL_PX[1:])) / 3.0},
+        # cv::FAST of the reference reads every pixel of every bin that needs features once (trackFeatures.cpp:196): that is
+        # the algorithmic traffic of the detector, however few of those pixels the kernel has to score
+        "lk_fast_pick": {"bound": "hbm", "bytes": n * px0 * bins_frac},
+        # the detector with every pixel scored: 72 packed u16x2 min / max per pixel pair on the ALU pipe
+        "lk_fast_band": {"bound": "int-alu", "bytes": n * px0 * bins_frac, "alu": fast_alu},
+        "lk_fast_kernel": {"bound": "int-alu", "bytes": n * px0 * bins_frac, "alu": fast_alu},
+    }
     kroof = {}
     for kname, kv in kb.items():
         k_ms = kv["ms_per_step"] / max(1.0, kv["launches_per_step"])
-        e = {"kernel_ms": k_ms}
-        if kname in alg_bytes:
-            a = alg_bytes[kname] / (k_ms * 1e-3) / 1e9
+        e = {"kernel_ms": k_ms, "bound": "latency"}
+        sp = next((v for pre, v in spec.items() if kname.startswith(pre)), None)
+        if sp and "flagged" not in kname:
+            e["bound"] = sp["bound"]
+            a = sp["bytes"] / (k_ms * 1e-3) / 1e9
             e["hbm"] = {"achieved": a, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": a / pk["hbm_gbs"],
-                        "algorithmic_bytes_per_launch": alg_bytes[kname], "traffic": ncu_traffic(kname, n, 512)}
-        if kname in alg_alu and "alu_packed_instr_per_s" in pk:
-            a = alg_alu[kname] / (k_ms * 1e-3)
-            e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed u16x2 min/max instr/s", "bins_scored_frac": bins_frac,
-                            "frac": a / pk["alu_packed_instr_per_s"], "algorithmic_instr_per_launch": alg_alu[kname]}
-        e["bound"] = {"lk_pyr_fused_kernel": "hbm", "lk_pyr_down_kernel": "hbm", "lk_fast_kernel": "int-alu"}.get(kname, "latency")
+                        "algorithmic_bytes_per_launch": sp["bytes"], "traffic": ncu_traffic(kname.split("<")[0], n, 512)}
+            if "alu" in sp and "alu_packed_instr_per_s" in pk:
+                a = sp["alu"] / (k_ms * 1e-3)
+                e["int_alu"] = {"achieved": a, "peak": pk["alu_packed_instr_per_s"], "unit": "packed u16x2 min/max instr/s",
+                                "bins_scored_frac": bins_frac, "frac": a / pk["alu_packed_instr_per_s"],
+                                "algorithmic_instr_per_launch": sp["alu"],
+                                "note": "algorithmic = the reference's cv::FAST: every pixel of every bin that needs features scored"}
         kroof[kname] = e
-    dom_bytes = alg_bytes.get(dom, n * LK_BYTES_PER_PAIR)
-    dom_ms = kb[dom]["ms_per_step"] / max(1.0, kb[dom]["launches_per_step"])
-    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+    step_bytes = n * LK_BYTES_PER_PAIR
+    step_roof = {"algorithmic_bytes_per_step": step_bytes, "achieved": step_bytes / (step_ms * 1e-3) / 1e9,
+                 "frac": step_bytes / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                 "note": "the whole calcFlow step against HBM: new frame read once, pyramid levels 1..3 written (SURVEY.md 8(d))"}
+    d = kroof[dom]
+    if d["bound"] == "int-alu" and "int_alu" in d:
+        roof = {"bound": "int-alu", "achieved": d["int_alu"]["achieved"], "peak": d["int_alu"]["peak"], "unit": d["int_alu"]["unit"],
+                "frac": d["int_alu"]["frac"], "traffic": d["hbm"]["traffic"], "peak_source": pk.get("alu_which", ""),
+                "algorithmic_instr_per_launch": d["int_alu"]["algorithmic_instr_per_launch"], "hbm": d["hbm"]}
+    elif d["bound"] == "hbm":
+        roof = {"bound": "hbm", "achieved": d["hbm"]["achieved"], "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": d["hbm"]["frac"],
+                "traffic": d["hbm"]["traffic"], "peak_source": pk["which"], "algorithmic_bytes_per_launch": d["hbm"]["algorithmic_bytes_per_launch"]}
+    else:
+        # the kernel that takes the most time is latency-bound (per-feature iterations / serial selection): it has no
+        # throughput roofline of its own; the step as a whole is stated against HBM instead
+        roof = {"bound": "hbm", "achieved": step_roof["achieved"], "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": step_roof["frac"],
+                "traffic": None, "peak_source": pk["which"], "algorithmic_bytes_per_launch": step_bytes,
+                "note": "dominant kernel %s is latency-bound; this is the whole step against HBM" % dom}
+    roof.update({"kernel": dom, "kernel_ms": d["kernel_ms"], "step": step_roof})
+    e2e_v = world * n * e_steps / (e2e_ms * 1e-3)
+    e2e_gbs = (fb + 4 * n) * e_steps / (e2e_ms * 1e-3) / 1e9
     r = {
         "value": world * n * args.steps / (ms * 1e-3), "ms_per_step": step_ms,
-        "config": {"workload": "lk640x480_features20 (BASELINE config 2 batched: OpticalFlowOpenCV::calcFlow, %d streams/GPU/launch, "
-                               "FAST + binned selection + 3-level pyramidal LK 9x9)" % n,
+        "timed_region": {"repeats": tm["repeats"], "steps_per_repeat": args.steps, "total_s": sum(tm["all_ms"]) * 1e-3,
+                         "ms_per_step_min": min(tm["all_ms"]) / args.steps, "ms_per_step_max": max(tm["all_ms"]) / args.steps},
+        "config": {"workload": workload_name("lk", n),
                    "streams_per_gpu": n, "image": "640x480", "features": LK_FEATURES, "output_rate": -1,
                    "l2": "frames rotate over %d buffers = %d MiB > 126 MB L2" % (rot, rot * fb >> 20),
                    "parallelism": "streams sharded across ranks, host gather, no collective"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / pk["hbm_gbs"], "traffic": ncu_traffic(dom, n, 512), "peak_source": pk["which"],
-                     "kernel": dom, "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
-                     "note": "dominant kernel by time; its binding roofline is in kernel_rooflines[kernel][bound] "
-                             "(lk_fast_kernel is integer-ALU bound, the HBM-bound kernel of the step is lk_pyr_fused_kernel)",
-                     "step": {"algorithmic_bytes_per_step": n * LK_BYTES_PER_PAIR,
-                              "achieved": n * LK_BYTES_PER_PAIR / (step_ms * 1e-3) / 1e9,
-                              "frac": n * LK_BYTES_PER_PAIR / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"]}},
+        "roofline": roof,
         "kernels": kb, "kernel_rooflines": kroof,
-        "e2e": {"value": world * n * e_steps / (e2e_ms * 1e-3), "unit": "frame-pairs/s",
+        "fast": {"bins_needing_features_frac": bins_frac,
+                 "per_step": {"bins_picked_lazily": lazy[0] / k_steps, "second_collect_passes": lazy[1] / k_steps,
+                              "bins_sent_to_complete_path": lazy[2] / k_steps, "stream_frames_on_complete_path": lazy[3] / k_steps}},
+        "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
-                "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)"},
+                "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
+                       (", then every rank's records gathered on rank 0 over the host (gloo) group" if world > 1 else ""),
+                "roofline": {"bound": "pcie-h2d", "achieved": e2e_gbs, "peak": h2d_gbs, "unit": "GB/s per GPU",
+                             "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
+                             "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},
         "single_stream_latency_us": lat_us,
-        "overlap": "value: the device entry point runs the two halves of the streams on two CUDA streams (8 launches per step, "
-                   "the latency-bound kernels of one half under the FAST kernel of the other); kernels / kernel_rooflines: the same "
-                   "steps with per-kernel event timing on, which runs them unsplit (4 launches per step, no overlap), so their sum "
-                   "exceeds ms_per_step; AOF_LK_SPLIT=1 times the unsplit step",
+        "overlap": "value: the device entry point pipelines two halves of the streams over two CUDA streams (the latency-bound "
+                   "kernels of one half under the throughput kernels of the other); kernels / kernel_rooflines: the same steps with "
+                   "per-kernel event timing on, which runs them unsplit, each kernel alone on the GPU (what a burst roofline "
+                   "needs), so their sum exceeds ms_per_step; AOF_LK_SPLIT=1 times the unsplit step",
         "gpu_launches": int(launches), "clocks": clocks, "dtype": "u8 (i32 / f32 in LK)",
     }
     if with_cpu:
-        r["cpu_baseline"] = cpu_lk(h_frames[:, :64], 12.0)
+        r["cpu_baseline"] = cpu_lk(np.array(h_frames), 12.0)
+        r["vs_cpu"] = {"e2e_over_cpu": e2e_v / r["cpu_baseline"]["value"], "device_resident_over_cpu": r["value"] / r["cpu_baseline"]["value"]}
     return r
 
 
@@ -647,6 +856,13 @@ def main():
         res["sad"] = run_sad_gpu(sad_args, rank, world, local, with_cpu)
         if res["sad"] is not None:
             res["sad"]["steps"] = sad_args.steps
+        if world == 8:
+            # BASELINE config 5 as written: 65 536 SAD streams over the 8 GPUs = 8192 per GPU (the weak-scaling series above
+            # keeps config 3's 4096 per GPU at every N)
+            c5 = run_sad_gpu(sad_args, rank, world, local, False, n_streams=SAD_STREAMS_CONFIG5, light=True)
+            if c5 is not None:
+                res["sad"]["config5"] = {k: c5[k] for k in ("value", "ms_per_step", "timed_region", "config", "roofline", "e2e", "gpu_launches")}
+                res["sad"]["config5"]["total_streams"] = world * SAD_STREAMS_CONFIG5
     if rank != 0:
         return
     p = res[primary]
@@ -654,7 +870,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": p["dtype"], "data": "synthetic", "config": p["config"], "roofline": p["roofline"],
             "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
-    for key in ("cpu_baseline", "single_stream_latency_us", "roofline_int_alu", "kernel_rooflines", "dense", "overlap"):
+    for key in ("timed_region", "cpu_baseline", "vs_cpu", "single_stream_latency_us", "kernel_rooflines", "fast", "dense", "overlap"):
         if key in p:
             line[key] = p[key]
     if args.workload == "both":

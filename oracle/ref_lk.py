@@ -79,10 +79,10 @@ def _cv2_backend():
             det.setThreshold(thr)
         kps = det.detect(np.ascontiguousarray(img))
         n = min(len(kps), cap)
-        out = np.ctypeslib.as_array(xyr, shape=(cap * 3,))
-        for i in range(n):
-            k = kps[i]
-            out[3 * i], out[3 * i + 1], out[3 * i + 2] = k.pt[0], k.pt[1], k.response
+        if n:
+            out = np.ctypeslib.as_array(xyr, shape=(cap * 3,))[: 3 * n].reshape(n, 3)
+            out[:, :2] = cv2.KeyPoint_convert(kps[:n])
+            out[:, 2] = np.fromiter((k.response for k in kps[:n]), np.float32, n)
         return n
 
     def pyrlk(prev, nxt, w, h, pts, n, out, status, win, max_level):

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""Lazy-FAST statistics on the bench's LK workload: per step, bins picked lazily / pool rebuilds / bins that failed /
-stream-frames sent to the complete path (aof_lk_lazy_stats).   python tools/lazy_probe.py [streams] [steps]"""
+"""Lazy-FAST statistics on the bench's LK workload: per step, bins picked lazily / second collecting passes / bins that
+failed / stream-frames sent to the complete path (aof_lk_lazy_stats).   python tools/lazy_probe.py [streams] [steps]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -26,3 +26,4 @@ for k in range(steps):
     print("step %d: lazy bins %d rebuilds %d failed bins %d streams->complete %d | bins needing FAST %.2f/16" %
           ((k,) + tuple(a - b for a, b in zip(st, last)) + (raw["fast_bins"].mean(),)))
     last = st
+f.close()
