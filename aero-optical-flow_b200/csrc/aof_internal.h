@@ -128,7 +128,7 @@ struct LkGeom {
 	int tun_pyr_v1;    // AOF_PYR_V1 = 1: the generic streaming kernel
 	int tun_fast_v1;   // AOF_FAST_V1 = 1: the tile FAST kernel
 	int tun_track_v1;  // AOF_TRACK_V1 = 1: the CTA-per-stream tracker
-	int tun_fast_lazy; // AOF_FAST_LAZY = 0: always score every pixel of the needed bins (default 1: lazy FAST)
+	int tun_fast_lazy; // AOF_FAST_LAZY = 0: score every pixel of the needed bins; 1: lazy arg-max (lk_fast_lazy.cu); 2 (default): masked band FAST
 };
 
 // level base pointers of one pyramid slot; level l of stream s is at lvl[l] + s * w[l] * h[l]
@@ -178,10 +178,10 @@ cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1
 cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
 				   int have_prev, cudaStream_t st);
 cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map,
-			   cudaStream_t st);
+			   cudaStream_t st, int masked = 0); // masked: only with the band kernel (lk_fast_band_supported)
 // banded FAST (lk_fast_band.cu); lk_fast_launch dispatches to it when the shape allows
 bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0);
-cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st);
+cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked = 0);
 // the same for the streams listed in s.full_list only (small persistent grid)
 cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);
 // lazy FAST (lk_fast_lazy.cu): the per-bin picks of initMorePoints without scoring every pixel
@@ -189,7 +189,7 @@ bool lk_fast_lazy_supported(const LkGeom &g, const uint8_t *l0);
 cudaError_t lk_fast_pick_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);
 // mode of lk_select_epilogue_launch: the complete path; the picks of lk_fast_pick_kernel (flags the streams that need
 // the complete path and leaves them untouched); the complete path for the flagged streams only
-enum { LK_SEL_COMPLETE = 0, LK_SEL_LAZY = 1, LK_SEL_FLAGGED = 2 };
+enum { LK_SEL_COMPLETE = 0, LK_SEL_LAZY = 1, LK_SEL_FLAGGED = 2, LK_SEL_MASKED = 3 };
 cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const uint32_t *t_us, aof_flow_out *out,
 				      aof_lk_raw *raw, int n, int have_feat_prev, int output_rate, float conf, float fx,
 				      float fy, const LkCamera &cam, cudaStream_t st, int mode = LK_SEL_COMPLETE);

@@ -163,7 +163,7 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	const size_t nN = (size_t)n_streams * N;
 	// every environment switch of this path is read here, once (never on a launch path)
 	g.tun_pyr_bands = env_int("AOF_PYR_BANDS", 0); g.tun_pyr_occ = env_int("AOF_PYR_OCC", 0);
-	g.tun_fast_lazy = env_int("AOF_FAST_LAZY", 1);
+	g.tun_fast_lazy = env_int("AOF_FAST_LAZY", 2);
 	g.tun_pyr_v1 = env_int("AOF_PYR_V1", 0); g.tun_fast_v1 = env_int("AOF_FAST_V1", 0); g.tun_track_v1 = env_int("AOF_TRACK_V1", 0);
 	h->tun_split = env_int("AOF_LK_SPLIT", 0); h->tun_parts = env_int("AOF_LK_PARTS", 0);
 	cudaError_t e;
@@ -289,13 +289,25 @@ static int run_pyr_track(aof_lk *h, int nxt, int first, int count, cudaStream_t 
 	return AOF_OK;
 }
 
-// lazy FAST (lk_fast_lazy.cu) where the shape allows, else the complete keypoint lists
+// How the keypoints of the bins that need features are found (AOF_FAST_LAZY, read at create):
+//   LK_SEL_MASKED (2, default)  the band kernel scoring only the pixels the first selection stage can accept
+//   LK_SEL_LAZY (1)             the lazy arg-max kernel (lk_fast_lazy.cu)
+//   LK_SEL_COMPLETE (0, and every shape the band kernel does not take)  every pixel scored
+// MASKED and LAZY hand the streams whose selection needs the second-chance pass to the complete path.
+static int fast_mode(const aof_lk *h, const uint8_t *l0)
+{
+	if (h->g.tun_fast_lazy == 2 && lk_fast_band_supported(h->g, l0)) return LK_SEL_MASKED;
+	if (h->g.tun_fast_lazy == 1 && lk_fast_lazy_supported(h->g, l0)) return LK_SEL_LAZY;
+	return LK_SEL_COMPLETE;
+}
+
 static int run_fast(aof_lk *h, int nxt, int first, int count, cudaStream_t st)
 {
 	const size_t f = (size_t)first;
 	const uint8_t *l0 = pyr_of(h, nxt, f).lvl[0];
-	if (lk_fast_lazy_supported(h->g, l0)) AOF_CUDA(lk_fast_pick_launch(h->g, l0, state_from(h->s, h->g, f), count, st));
-	else AOF_CUDA(lk_fast_launch(h->g, l0, state_from(h->s, h->g, f), count, nullptr, st));
+	const int mode = fast_mode(h, l0);
+	if (mode == LK_SEL_LAZY) AOF_CUDA(lk_fast_pick_launch(h->g, l0, state_from(h->s, h->g, f), count, st));
+	else AOF_CUDA(lk_fast_launch(h->g, l0, state_from(h->s, h->g, f), count, nullptr, st, mode == LK_SEL_MASKED));
 	return AOF_OK;
 }
 
@@ -305,15 +317,16 @@ static int run_select(aof_lk *h, const uint32_t *d_t_us, aof_flow_out *d_out, ao
 	const size_t f = (size_t)first;
 	const LkState sv = state_from(h->s, h->g, f);
 	const uint8_t *l0 = pyr_of(h, h->cur ^ 1, f).lvl[0];
-	const bool lazy = lk_fast_lazy_supported(h->g, l0);
-	// lazy: the selection takes the picks, flags the streams whose second-chance pass needs every keypoint; those (usually
-	// none) then go through the complete FAST and the complete selection
+	const int mode = fast_mode(h, l0);
+	const bool lazy = mode != LK_SEL_COMPLETE;
+	// masked / lazy: the selection flags the streams whose second-chance pass needs every keypoint; those (usually none)
+	// then go through the complete FAST and the complete selection
 	for (int pass = 0; pass < (lazy ? 2 : 1); pass++) {
 		if (pass == 1) AOF_CUDA(lk_fast_band_flagged_launch(h->g, l0, sv, count, st));
 		AOF_CUDA(lk_select_epilogue_launch(h->g, sv, d_t_us + f, d_out + f, d_raw ? d_raw + f : nullptr, count,
 						   h->have_feat_prev ? 1 : 0, h->p.output_rate, h->p.confidence_multiplier,
 						   h->p.focal_length_x, h->p.focal_length_y, h->cam, st,
-						   !lazy ? LK_SEL_COMPLETE : pass == 0 ? LK_SEL_LAZY : LK_SEL_FLAGGED));
+						   pass == 0 ? mode : LK_SEL_FLAGGED));
 	}
 	return AOF_OK;
 }

@@ -20,6 +20,15 @@
 //   * survivors are collected in shared memory and appended to the bin's list with one global
 //     atomic per CTA.  Entry = score << 24 | y << 12 | x, bin-local (order in the list is free:
 //     the selection kernel uses the total order score desc, raster asc).
+//   * MASKED mode (the default of the calcFlow path): the first stage of initMorePoints only ever accepts keypoints
+//     that keep the Chebyshev distance `dist` from every active point (trackFeatures.cpp:207-241), and on a 640-px
+//     frame the exclusion squares (2 dist - 1 = 159 px) cover ~70 % of a bin that needs features.  A pixel pair is
+//     scored only where the mask of the band has a bit: mask = scoring area minus the exclusion squares SHRUNK by one
+//     pixel, so that every free pixel still sees the exact responses of its 8 neighbours in the suppression.  Bands
+//     with an empty mask return before loading anything.  The lists then hold exactly the keypoints of the free
+//     region (plus possibly false maxima in the one-pixel ring, all of which the selection rejects as too close);
+//     a stream whose selection needs the second-chance pass (:266-304: every keypoint, dist / 2) is flagged by the
+//     selection kernel and redone unmasked by lk_fast_band_flagged_kernel.
 // Needs bw % 4 == 0, W % 4 == 0, a 4-byte aligned batch and bw <= 512; other shapes use lk_fast_kernel.
 #include <cstdlib>
 
@@ -32,6 +41,16 @@ constexpr int FB_ROWS = 38;             // output rows per band (a 120-row bin h
 constexpr int FB_SROWS = FB_ROWS + 2;   // response rows (one above, one below for the suppression)
 constexpr int FB_PROWS = FB_ROWS + 8;   // pixel rows
 constexpr int FB_MAX_GROUPS = 20;       // row groups: thread = (group, pair column); THREADS / (bw / 2) of them
+constexpr int FB_MWORDS = 17;           // mask words per response row (bw <= 512, + 1 for the pair that straddles)
+
+// bits [lo, hi] (inclusive, pixel columns) that fall into the 32-bit word starting at column `base`
+__device__ __forceinline__ uint32_t fb_bits(int lo, int hi, int base)
+{
+	lo = max(lo - base, 0);
+	hi = min(hi - base, 31);
+	if (lo > hi) return 0u;
+	return (0xFFFFFFFFu >> (31 - hi + lo)) << lo;
+}
 
 __device__ __forceinline__ uint32_t fb_mn(uint32_t a, uint32_t b) { return __vminu2(a, b); }
 __device__ __forceinline__ uint32_t fb_mx(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
@@ -82,7 +101,7 @@ __device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint3
 // 640-px frame: every ring tap is then an immediate offset of one base address), 0 = run time (P_rt)
 template <int THREADS, int PC>
 __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restrict__ l0, const LkState &s, uint8_t *__restrict__ score_map,
-					 int bands, int P_rt, int list_cap, size_t stream, int bin, int band)
+					 int bands, int P_rt, int list_cap, size_t stream, int bin, int band, int masked)
 {
 	const int P = PC ? PC : P_rt;
 	extern __shared__ __align__(16) uint32_t fb_smem[];
@@ -100,6 +119,37 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	const int y0 = 3 + band * FB_ROWS;                            // first output row of the band (bin coordinates)
 	const int y1 = min(y0 + FB_ROWS, bh - 3);                     // one past the last
 	const int tid = threadIdx.x;
+	// ---- MASKED: which pixels of the band's response rows can matter to the first selection stage
+	__shared__ uint32_t sM[FB_SROWS][FB_MWORDS];
+	__shared__ short2 s_ex[LK_MAX_FEATURES];
+	__shared__ int s_nex;
+	if (masked) {
+		const int dist = g.dist, N = g.n_feat;
+		if (tid == 0) s_nex = 0;
+		__syncthreads();
+		const int npc = s.n_prev_corners[stream];
+		for (int k = tid; k < npc; k += THREADS) {
+			if (!s.prev_status[stream * N + k]) continue;
+			const float2 p = s.prev_corners[stream * N + k];          // int-truncated as in trackFeatures.cpp:212-224
+			const int ex = (int)p.x - c0, ey = (int)p.y - r0;         // bin-local
+			if (ex > -dist && ex < bw - 1 + dist && ey > y0 - 1 - dist && ey < y1 + dist)
+				s_ex[atomicAdd(&s_nex, 1)] = make_short2((short)ex, (short)ey);
+		}
+		__syncthreads();
+		const int nex = s_nex, fmw = (bw + 31) >> 5, rows = y1 - y0 + 2;
+		uint32_t any = 0;
+		for (int i = tid; i < rows * FB_MWORDS; i += THREADS) {
+			const int sr = i / FB_MWORDS, w = i - sr * FB_MWORDS, y = y0 - 1 + sr;
+			uint32_t m = (w < fmw && y >= 3 && y < bh - 3) ? fb_bits(3, bw - 4, 32 * w) : 0u;
+			for (int k = 0; k < nex && m; k++) {
+				const short2 e = s_ex[k];
+				if (abs(e.y - y) < dist - 1) m &= ~fb_bits(e.x - dist + 2, e.x + dist - 2, 32 * w);
+			}
+			sM[sr][w] = m;
+			any |= m;
+		}
+		if (!__syncthreads_or(any != 0)) return;                      // nothing of this band can be accepted
+	}
 	if (tid == 0) s_n = 0;
 	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
 
@@ -153,7 +203,12 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 		const int sr_lo = max(0, 4 - y0), sr_hi = min(n_srow, bh - 2 - y0);
 		for (int sr = grp; sr < n_srow; sr += ngrp) {
 			uint32_t b = 0u;
-			if (sr >= sr_lo && sr < sr_hi) {
+			bool on = sr >= sr_lo && sr < sr_hi;
+			if (on && masked) {
+				const int x = 2 * j + 1;
+				on = (((sM[sr][x >> 5] >> (x & 31)) | (sM[sr][(x + 1) >> 5] >> ((x + 1) & 31))) & 1u) != 0;
+			}
+			if (on) {
 				const uint32_t m = fb_score_pair(sA + (sr + 3) * P + j, sB + (sr + 3) * P + j, P);
 				b = col_ok ? fb_mx(m, lim) - lim : 0u;
 			}
@@ -226,10 +281,10 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 template <int THREADS, int PC>
 __global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
-		    int list_cap)
+		    int list_cap, int masked)
 {
 	const int bin = blockIdx.x / bands;
-	fb_body<THREADS, PC>(g, l0, s, score_map, bands, P_rt, list_cap, blockIdx.y, bin, blockIdx.x - bin * bands);
+	fb_body<THREADS, PC>(g, l0, s, score_map, bands, P_rt, list_cap, blockIdx.y, bin, blockIdx.x - bin * bands, masked);
 }
 
 // The complete keypoint lists of the FLAGGED streams only (lazy FAST, lk_fast_lazy.cu: the selection kernel lists the
@@ -243,7 +298,7 @@ lk_fast_band_flagged_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s,
 	const int per_stream = LK_BINS * bands;
 	for (int w = blockIdx.x; w < n_flag * per_stream; w += gridDim.x) {
 		const int f = w / per_stream, r = w - f * per_stream, bin = r / bands;
-		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)s.full_list[f], bin, r - bin * bands);
+		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)s.full_list[f], bin, r - bin * bands, 0);
 		__syncthreads();                                    // the next item reuses the shared-memory tiles and counters
 	}
 }
@@ -266,7 +321,7 @@ bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0)
 }
 
 template <int THREADS, int PC>
-static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
+static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked)
 {
 	int P, cap;
 	const size_t smem = fb_smem_bytes(g, P, cap);
@@ -280,7 +335,7 @@ static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &
 	}
 	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
 	dim3 grid(LK_BINS * bands, n);
-	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
+	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap, score_map ? 0 : masked);
 	return cudaGetLastError();
 }
 
@@ -319,15 +374,15 @@ cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, cons
 	return fb_launch_flagged<1024, 0>(g, l0, s, n, st);
 }
 
-cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
+cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked)
 {
 	const int npc = g.bw / 2;
 	// 640-px frames: pitch known at compile time.  (640 threads per CTA was measured 24 % slower: 5 rows per thread do
 	// not amortise the per-thread set-up.)
-	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st);
-	if (4 * npc <= 320) return fb_launch<320, 0>(g, l0, s, n, score_map, st);
-	if (4 * npc <= 640) return fb_launch<640, 0>(g, l0, s, n, score_map, st);
-	return fb_launch<1024, 0>(g, l0, s, n, score_map, st);
+	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st, masked);
+	if (4 * npc <= 320) return fb_launch<320, 0>(g, l0, s, n, score_map, st, masked);
+	if (4 * npc <= 640) return fb_launch<640, 0>(g, l0, s, n, score_map, st, masked);
+	return fb_launch<1024, 0>(g, l0, s, n, score_map, st, masked);
 }
 
 } // namespace aof

@@ -702,7 +702,7 @@ lk_fast_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__r
 	}
 }
 
-cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
+cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked)
 {
 	if (n <= 0) return cudaSuccess;
 	const int tiles_x = (g.bw + FT_TW - 1) / FT_TW, tiles_y = (g.bh + FT_TH - 1) / FT_TH;
@@ -711,7 +711,7 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 	KernelTimer kt(KID_LK_FAST, st, !band ? "lk_fast_kernel" : g.bw == 160 ? "lk_fast_band_kernel<320,84>" : "lk_fast_band_kernel");
 	if (band) {
 		count_launch();
-		return lk_fast_band_launch(g, l0, s, n, score_map, st);
+		return lk_fast_band_launch(g, l0, s, n, score_map, st, masked);
 	}
 	if (g.w[0] % 16 == 0 && (reinterpret_cast<uintptr_t>(l0) & 3) == 0)
 		lk_fast_kernel<true><<<grid, FT_THREADS, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
@@ -927,9 +927,11 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 			}
 		}
 		__syncthreads();
-		if (mode == LK_SEL_LAZY && (!s_done || s_lazy_fail)) {
+		if ((mode == LK_SEL_LAZY || mode == LK_SEL_MASKED) && (!s_done || s_lazy_fail)) {
 			// the second-chance pass needs every keypoint of every processed bin: hand the stream to the complete path
 			// (lk_fast_band_flagged_kernel, then this kernel in LK_SEL_FLAGGED mode); no state has been written yet
+			// (MASKED: the lists hold the free region's keypoints only; the complete pass appends from zero)
+			if (mode == LK_SEL_MASKED && tid < LK_BINS) s.kp_count[stream * LK_BINS + tid] = 0;
 			if (tid == 0) {
 				s.need_full[stream] = 1;
 				atomicAdd(&s.lz_stats[3], 1ull);

@@ -273,10 +273,12 @@ def _run_sequences(pkg, frames, w, h, nf, rate=-1):
     return outs, stats
 
 
+@pytest.mark.parametrize("mode", ["2", "1"])
 @pytest.mark.parametrize("w,h,nf", [(640, 480, 20), (320, 240, 50), (128, 128, 20), (256, 192, 100)])
-def test_lazy_fast_equals_complete_path(pkg, w, h, nf, monkeypatch):
-    """lk_fast_pick_kernel (lazy FAST: bound, pool, exact scores of the candidates only) against the complete keypoint
-    lists (AOF_FAST_LAZY=0), byte for byte: outputs, diagnostics and the whole tracker state, frame by frame; includes
+def test_lazy_fast_equals_complete_path(pkg, w, h, nf, mode, monkeypatch):
+    """The two shortcuts of the detector -- AOF_FAST_LAZY=2 (default): lk_fast_band_kernel scoring only the pixels outside
+    the exclusion squares of the active points; =1: lk_fast_pick_kernel (bound, pool, exact scores of the candidates
+    only) -- against the complete keypoint lists (AOF_FAST_LAZY=0), byte for byte: outputs, diagnostics and the whole tracker state, frame by frame; includes
     a scene cut (every feature lost: all 16 bins requested again) and flat frames (no corner anywhere)."""
     n, T = 12, 9
     rng = np.random.default_rng(w + nf)
@@ -286,11 +288,11 @@ def test_lazy_fast_equals_complete_path(pkg, w, h, nf, monkeypatch):
     frames[5, :4] = frames[0, 4:8]                       # scene cut for four streams
     frames[6, 8] = 90                                    # a flat frame
     frames[:, 9] = (frames[:, 9] // 8) + 100             # a low-contrast stream: bounds below any learnt floor
-    monkeypatch.setenv("AOF_FAST_LAZY", "1")
+    monkeypatch.setenv("AOF_FAST_LAZY", mode)
     lazy, stats = _run_sequences(pkg, frames, w, h, nf)
     monkeypatch.setenv("AOF_FAST_LAZY", "0")
     full, stats0 = _run_sequences(pkg, frames, w, h, nf)
-    assert stats0 == (0, 0, 0, 0) and stats[0] > 0, (stats, stats0)
+    assert stats0 == (0, 0, 0, 0) and (stats[0] > 0 or mode == "2"), (stats, stats0)
     for k in range(T):
         assert lazy[k][0].tobytes() == full[k][0].tobytes(), k
         assert lazy[k][1].tobytes() == full[k][1].tobytes(), k
@@ -305,13 +307,15 @@ def test_lazy_fast_equals_complete_path(pkg, w, h, nf, monkeypatch):
             assert (r["quality"][i], r["flow_x"][i], r["flow_y"][i]) == (q, np.float32(fx), np.float32(fy)), (i, k)
 
 
-def test_lazy_fast_second_chance_goes_through_the_complete_path(pkg):
+@pytest.mark.parametrize("mode", ["2", "1"])
+def test_lazy_fast_second_chance_goes_through_the_complete_path(pkg, mode, monkeypatch):
     """sparse blobs: fewer acceptable keypoints than requests, so initMorePoints' second-chance pass runs
     (trackFeatures.cpp:266-304); the lazy selection must hand those streams to the complete path and still equal the oracle"""
     from test_ref_lk import blob_sequence
     w, h, nf, T = 320, 240, 33, 6
     seqs = [blob_sequence(T, w, h, 2, -1, 41 + i) for i in range(4)]
     frames = np.stack([np.stack([seqs[i][k] for i in range(4)]) for k in range(T)])
+    monkeypatch.setenv("AOF_FAST_LAZY", mode)
     got, stats = _run_sequences(pkg, frames, w, h, nf)
     assert stats[3] > 0, stats                           # the fallback really ran
     for i in range(4):
