@@ -122,10 +122,12 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	// ---- MASKED: which pixels of the band's response rows can matter to the first selection stage
 	__shared__ uint32_t sM[FB_SROWS][FB_MWORDS];
 	__shared__ short2 s_ex[LK_MAX_FEATURES];
-	__shared__ int s_nex;
+	__shared__ uint16_t s_units[FB_SROWS * FB_MWORDS];            // live (response row << 8 | 16-pair segment) units
+	__shared__ int s_nex, s_nunits, s_rlo, s_rhi;
+	int rlo = 0, rhi = FB_SROWS;                                  // response rows with a live unit (masked only)
 	if (masked) {
 		const int dist = g.dist, N = g.n_feat;
-		if (tid == 0) s_nex = 0;
+		if (tid == 0) { s_nex = 0; s_nunits = 0; s_rlo = FB_SROWS; s_rhi = -1; }
 		__syncthreads();
 		const int npc = s.n_prev_corners[stream];
 		for (int k = tid; k < npc; k += THREADS) {
@@ -149,6 +151,30 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 			any |= m;
 		}
 		if (!__syncthreads_or(any != 0)) return;                      // nothing of this band can be accepted
+		// The free part of a bin is a few rectangles: with the static (row group, pair column) mapping below one warp
+		// of a CTA would score all its rows and the others none.  Units of 16 pixel pairs x 1 response row with a mask
+		// bit are listed instead and dealt to the half-warps; the rows outside [rlo, rhi] are neither loaded nor
+		// searched for maxima.  Responses of the pairs that are not scored are 0.
+		const int nseg = ((bw >> 1) + 15) >> 4;
+		const int P_ = PC ? PC : P_rt;
+		uint32_t *zS = fb_smem + 2 * FB_PROWS * P_;
+		for (int i = tid; i < rows * P_; i += THREADS) zS[i] = 0u;
+		const int lo_sr = max(0, 4 - y0), hi_sr = min(rows, bh - 2 - y0);
+		for (int i = tid; i < rows * nseg; i += THREADS) {
+			const int sr = i / nseg, seg = i - sr * nseg;
+			if (sr >= lo_sr && sr < hi_sr && ((sM[sr][seg] >> 1) | (sM[sr][seg + 1] << 31))) {   // pixels 32 seg + 1 .. 32 seg + 32
+				s_units[atomicAdd(&s_nunits, 1)] = (uint16_t)((sr << 8) | seg);
+				atomicMin(&s_rlo, sr);
+				atomicMax(&s_rhi, sr);
+			}
+		}
+		__syncthreads();
+		rlo = s_rlo; rhi = s_rhi;
+		if (tid == 0 && s.lz_stats) { // diagnostics (aof_lk_lazy_stats): band CTAs that scored anything, their live units
+			atomicAdd(&s.lz_stats[0], 1ull);
+			atomicAdd(&s.lz_stats[1], (unsigned long long)s_nunits);
+		}
+		if (rhi < 0) return;                                          // (mask bits only in rows that carry no response)
 	}
 	if (tid == 0) s_n = 0;
 	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
@@ -169,7 +195,8 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 #pragma unroll
 		for (int k = 0; k < LD_ROUNDS; k++) {
 			const int y = y0 - 4 + t;
-			const bool on = t < n_prow && y >= 0 && y < bh;       // rows -1 and bh only feed responses that are not computed
+			// rows -1 and bh only feed responses that are not computed; masked: response row sr reads tile rows sr .. sr + 6
+			const bool on = t < n_prow && y >= 0 && y < bh && t >= rlo && t <= rhi + 6;
 			tt[k] = on ? t : -1; qq[k] = q;
 			const uint32_t *row = img32 + (on ? y * W4 : 0);      // 32-bit offsets: a bin is far below 2^31 bytes
 			w0[k] = __ldg(row + q);
@@ -197,18 +224,23 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	const bool col_ok = grp < ngrp && j >= 1 && j <= npc - 3;
 	const int n_srow = y1 - y0 + 2;
 	const uint32_t lim = (256u + (uint32_t)g.fast_thr) * 0x00010001u;
-	if (grp < ngrp) {
+	if (masked) {
+		const int half = (tid >> 4) & 1, l16 = tid & 15, nunits = s_nunits;
+		const int jj0 = l16;
+		for (int u = 2 * (tid >> 5) + half; u < nunits; u += 2 * (THREADS / 32)) {
+			const int sr = s_units[u] >> 8, jj = 16 * (s_units[u] & 255) + jj0;
+			if (jj < npc) {
+				const uint32_t m = fb_score_pair(sA + (sr + 3) * P + jj, sB + (sr + 3) * P + jj, P);
+				sS[sr * P + jj] = (jj >= 1 && jj <= npc - 3) ? fb_mx(m, lim) - lim : 0u;
+			}
+		}
+	} else if (grp < ngrp) {
 		// rows of the band whose response exists (3 <= y < bh - 3); the others (first / last band only) are zero.
 		// Columns outside [1, npc - 3] run the network on the pitch padding and drop the result.
 		const int sr_lo = max(0, 4 - y0), sr_hi = min(n_srow, bh - 2 - y0);
 		for (int sr = grp; sr < n_srow; sr += ngrp) {
 			uint32_t b = 0u;
-			bool on = sr >= sr_lo && sr < sr_hi;
-			if (on && masked) {
-				const int x = 2 * j + 1;
-				on = (((sM[sr][x >> 5] >> (x & 31)) | (sM[sr][(x + 1) >> 5] >> ((x + 1) & 31))) & 1u) != 0;
-			}
-			if (on) {
+			if (sr >= sr_lo && sr < sr_hi) {
 				const uint32_t m = fb_score_pair(sA + (sr + 3) * P + j, sB + (sr + 3) * P + j, P);
 				b = col_ok ? fb_mx(m, lim) - lim : 0u;
 			}
@@ -220,8 +252,9 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	// ---- 3 x 3 non-maximum suppression, each thread walking down its share of the band's rows
 	if (col_ok) {
 		const int n_out = y1 - y0;
-		const int chunk = (n_out + ngrp - 1) / ngrp;
-		const int ra = 1 + grp * chunk, rb = min(ra + chunk, n_out + 1);   // response rows of this thread's outputs
+		const int oa = max(1, rlo), ob = min(n_out + 1, rhi + 1);          // (masked: the rows with a live unit only)
+		const int chunk = (max(ob - oa, 0) + ngrp - 1) / ngrp;
+		const int ra = oa + grp * chunk, rb = min(ra + chunk, ob);         // response rows of this thread's outputs
 		const uint32_t *col = sS + j;
 		auto hmax = [&](int sr, uint32_t &c, uint32_t &side) -> uint32_t {
 			const uint32_t l = col[sr * P - 1], r = col[sr * P + 1];
