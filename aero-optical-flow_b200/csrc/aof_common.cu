@@ -80,7 +80,7 @@ namespace aof {
 static const char *g_kernel_names[KID_COUNT] = {
 	"sad_flow_kernel", "px4_epilogue_kernel", "lk_pyr_down_kernel", "lk_track_update_kernel", "lk_fast_kernel",
 	"lk_select_epilogue_kernel", "lk_track_points_kernel", "sad_dense_kernel", "gftt_min_eig_kernel", "gftt_select_kernel",
-	"lk_pyr_fused_kernel", "lk_fast_pick_kernel", "lk_fast_band_flagged_kernel",
+	"lk_pyr_fused_kernel", "lk_fast_pick_kernel", "lk_fast_band_flagged_kernel", "lk_fast_plan_kernel",
 };
 
 struct TimingState {

@@ -70,7 +70,7 @@ void count_launch(uint64_t n = 1);
 // kernel ids of the optional per-kernel event timing (aof_timing_* in include/aof.h)
 enum KernelId {
 	KID_SAD_FLOW = 0, KID_PX4_EPILOGUE, KID_LK_PYR_DOWN, KID_LK_TRACK_UPDATE, KID_LK_FAST, KID_LK_SELECT_EPILOGUE,
-	KID_LK_TRACK_POINTS, KID_SAD_DENSE, KID_GFTT_MIN_EIG, KID_GFTT_SELECT, KID_LK_PYR_FUSED, KID_LK_FAST_PICK, KID_LK_FAST_FLAGGED, KID_COUNT
+	KID_LK_TRACK_POINTS, KID_SAD_DENSE, KID_GFTT_MIN_EIG, KID_GFTT_SELECT, KID_LK_PYR_FUSED, KID_LK_FAST_PICK, KID_LK_FAST_FLAGGED, KID_LK_FAST_PLAN, KID_COUNT
 };
 
 // brackets one launch with two events when timing is enabled; a no-op otherwise
@@ -122,6 +122,8 @@ struct LkGeom {
 	int dist;         // binWidth / targetFeaturesPerBin
 	int kp_cap;       // keypoint-list capacity per bin
 	int fast_thr;     // 10
+	int fb_bands;     // 38-row bands per bin of the band FAST kernel (lk_fast_band.cu)
+	int fb_ucap;      // live-unit capacity of one band: 40 response rows x segments of 16 pixel pairs
 	// A/B and tuning switches, read from the environment ONCE in aof_lk_create (env_int)
 	int tun_pyr_bands; // AOF_PYR_BANDS: forced band count of the streaming pyramid kernel (0 = auto)
 	int tun_pyr_occ;   // AOF_PYR_OCC: CTAs per SM the pyramid kernel is compiled for (16 / 20 / 24)
@@ -161,6 +163,13 @@ struct LkState {
 	int *full_list;         // [n]       range-local indices of the flagged streams
 	unsigned long long *lz_stats; // [4] diagnostics, whole handle: bins picked lazily, pool rebuilds, bins that overflowed
 	                              //     the lazy buffers, streams sent to the complete path
+	                              //     (masked FAST: [0] bands with work, [1] their live units)
+	// masked band FAST (lk_fast_band.cu): lk_fast_plan_kernel lists, per (stream, bin, band), the units of 16 pixel
+	// pairs x 1 response row that the first selection stage can accept from, and the bands that have any
+	uint16_t *plan_units;   // [n * 16 * fb_bands * fb_ucap]  response row << 8 | segment
+	uint32_t *plan_hdr;     // [n * 16 * fb_bands]  units | first live row << 16 | last live row << 24
+	uint32_t *work_list;    // [n * 16 * fb_bands]  range-local (stream * 16 + bin) * fb_bands + band of the bands with work
+	int *n_work;            // [n]       element 0 of a range counts its work items (reset by the selection kernel)
 };
 
 // camera model of setCameraMatrix / setCameraDistortion (flow_opencv.cpp:72-87); on only when both were set
@@ -178,12 +187,15 @@ cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1
 cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkPyr &next, const LkState &s, int n,
 				   int have_prev, cudaStream_t st);
 cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map,
-			   cudaStream_t st, int masked = 0); // masked: only with the band kernel (lk_fast_band_supported)
+			   cudaStream_t st);
 // banded FAST (lk_fast_band.cu); lk_fast_launch dispatches to it when the shape allows
 bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0);
-cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked = 0);
+cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st);
 // the same for the streams listed in s.full_list only (small persistent grid)
 cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);
+// masked band FAST: the plan (live units per band, work list), then a persistent grid over the work list
+bool lk_fast_masked_supported(const LkGeom &g, const uint8_t *l0);
+cudaError_t lk_fast_masked_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);
 // lazy FAST (lk_fast_lazy.cu): the per-bin picks of initMorePoints without scoring every pixel
 bool lk_fast_lazy_supported(const LkGeom &g, const uint8_t *l0);
 cudaError_t lk_fast_pick_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st);

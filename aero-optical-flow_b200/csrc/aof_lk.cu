@@ -65,6 +65,8 @@ static LkState state_from(const LkState &s, const LkGeom &g, size_t first)
 	v.lk_next += first * N; v.lk_stat += first * N; v.ticket += first;
 	v.lz_pick += first * LK_BINS * LK_MAX_TPB; v.lz_npick += first * LK_BINS; v.lz_floor += first * LK_BINS;
 	v.need_full += first; v.n_full += first; v.full_list += first;
+	const size_t nb = (size_t)LK_BINS * g.fb_bands;
+	v.plan_units += first * nb * g.fb_ucap; v.plan_hdr += first * nb; v.work_list += first * nb; v.n_work += first;
 	return v;
 }
 
@@ -100,6 +102,7 @@ static int reset_state(aof_lk *h)
 	AOF_CUDA(cudaMemset(h->s.lz_floor, 0, sizeof(int) * LK_BINS * h->n));
 	AOF_CUDA(cudaMemset(h->s.need_full, 0, sizeof(int) * h->n));
 	AOF_CUDA(cudaMemset(h->s.n_full, 0, sizeof(int) * h->n));
+	AOF_CUDA(cudaMemset(h->s.n_work, 0, sizeof(int) * h->n));
 	AOF_CUDA(cudaMemset(h->s.lz_stats, 0, sizeof(unsigned long long) * 4));
 	h->have_prev = h->have_feat_prev = false;
 	h->cur = 0;
@@ -139,6 +142,8 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	LkGeom &g = h->g;
 	g.n_feat = N; g.bw = W / 4; g.bh = H / 4; g.tpb = tpb; g.dist = g.bw / tpb; g.fast_thr = 10;
 	g.kp_cap = ((g.bw + 1) / 2) * ((g.bh + 1) / 2);
+	g.fb_bands = g.bh > 6 ? (g.bh - 6 + 37) / 38 : 1;
+	g.fb_ucap = 40 * ((g.bw / 2 + 15) / 16);
 	if (g.bw > 4096 || g.bh > 4096) { // keypoint entries carry 12-bit bin-local coordinates
 		delete h;
 		set_error("frame %dx%d too large: bins above 4096 px", W, H);
@@ -205,6 +210,10 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	    (e = cudaMalloc(&h->s.n_full, sizeof(int) * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.full_list, sizeof(int) * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.lz_stats, sizeof(unsigned long long) * 4)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.plan_units, sizeof(uint16_t) * LK_BINS * g.fb_bands * (size_t)g.fb_ucap * n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.plan_hdr, sizeof(uint32_t) * LK_BINS * g.fb_bands * (size_t)n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.work_list, sizeof(uint32_t) * LK_BINS * g.fb_bands * (size_t)n_streams)) != cudaSuccess ||
+	    (e = cudaMalloc(&h->s.n_work, sizeof(int) * n_streams)) != cudaSuccess ||
 	    (e = cudaMalloc(&h->s.kp, sizeof(uint32_t) * LK_BINS * (size_t)g.kp_cap * n_streams)) != cudaSuccess) {
 		set_error("aof_lk_create: %s", cudaGetErrorString(e));
 		aof_lk_destroy(h);
@@ -228,6 +237,7 @@ void aof_lk_destroy(aof_lk *h)
 	cudaFree(h->s.lk_next); cudaFree(h->s.lk_stat); cudaFree(h->s.ticket);
 	cudaFree(h->s.lz_pick); cudaFree(h->s.lz_npick); cudaFree(h->s.lz_floor);
 	cudaFree(h->s.need_full); cudaFree(h->s.n_full); cudaFree(h->s.full_list); cudaFree(h->s.lz_stats);
+	cudaFree(h->s.plan_units); cudaFree(h->s.plan_hdr); cudaFree(h->s.work_list); cudaFree(h->s.n_work);
 	cudaFree(h->d_frames[0]); cudaFree(h->d_frames[1]);
 	cudaFreeHost(h->h_stage); cudaFreeHost(h->h_t); cudaFreeHost(h->h_out); cudaFreeHost(h->h_raw);
 	cudaFree(h->d_t); cudaFree(h->d_out); cudaFree(h->d_raw);
@@ -296,7 +306,7 @@ static int run_pyr_track(aof_lk *h, int nxt, int first, int count, cudaStream_t 
 // MASKED and LAZY hand the streams whose selection needs the second-chance pass to the complete path.
 static int fast_mode(const aof_lk *h, const uint8_t *l0)
 {
-	if (h->g.tun_fast_lazy == 2 && lk_fast_band_supported(h->g, l0)) return LK_SEL_MASKED;
+	if (h->g.tun_fast_lazy == 2 && lk_fast_masked_supported(h->g, l0)) return LK_SEL_MASKED;
 	if (h->g.tun_fast_lazy == 1 && lk_fast_lazy_supported(h->g, l0)) return LK_SEL_LAZY;
 	return LK_SEL_COMPLETE;
 }
@@ -307,7 +317,8 @@ static int run_fast(aof_lk *h, int nxt, int first, int count, cudaStream_t st)
 	const uint8_t *l0 = pyr_of(h, nxt, f).lvl[0];
 	const int mode = fast_mode(h, l0);
 	if (mode == LK_SEL_LAZY) AOF_CUDA(lk_fast_pick_launch(h->g, l0, state_from(h->s, h->g, f), count, st));
-	else AOF_CUDA(lk_fast_launch(h->g, l0, state_from(h->s, h->g, f), count, nullptr, st, mode == LK_SEL_MASKED));
+	else if (mode == LK_SEL_MASKED) AOF_CUDA(lk_fast_masked_launch(h->g, l0, state_from(h->s, h->g, f), count, st));
+	else AOF_CUDA(lk_fast_launch(h->g, l0, state_from(h->s, h->g, f), count, nullptr, st));
 	return AOF_OK;
 }
 
@@ -358,7 +369,12 @@ int aof_lk_calc_flow_device(aof_lk *h, const uint8_t *d_imgs, const uint32_t *d_
 	int parts = h->tun_parts > 0 ? h->tun_parts : 2;
 	if (parts > LK_MAX_PARTS) parts = LK_MAX_PARTS;
 	if (parts > h->n) parts = h->n;
-	const bool pipelined = (h->tun_split == 0 ? h->n >= 256 : h->tun_split >= 2) && parts >= 2 && !timing_on() && h->ev_trk[LK_MAX_PARTS - 1];
+	// Measured with the masked detector (r2r, 512 streams): one pass 0.499 ms, 2 parts 0.563, 3 parts 0.562, 4 parts 0.601 --
+	// its band kernel is a persistent grid that holds every CTA slot it can get, so a second part's latency-bound
+	// kernels find no room beside it and the parts only add launches.  The pipeline stays the default for the complete
+	// and the lazy detector (short CTAs that leave slots as they finish).
+	const bool auto_split = h->n >= 256 && fast_mode(h, d_imgs) != LK_SEL_MASKED;
+	const bool pipelined = (h->tun_split == 0 ? auto_split : h->tun_split >= 2) && parts >= 2 && !timing_on() && h->ev_trk[LK_MAX_PARTS - 1];
 	cudaStream_t st = (cudaStream_t)cuda_stream;
 	int rc = AOF_OK;
 	if (!pipelined) rc = run_range(h, nxt, d_t_us, d_out, d_raw, 0, h->n, st);

@@ -24,8 +24,11 @@
 //     that keep the Chebyshev distance `dist` from every active point (trackFeatures.cpp:207-241), and on a 640-px
 //     frame the exclusion squares (2 dist - 1 = 159 px) cover ~70 % of a bin that needs features.  A pixel pair is
 //     scored only where the mask of the band has a bit: mask = scoring area minus the exclusion squares SHRUNK by one
-//     pixel, so that every free pixel still sees the exact responses of its 8 neighbours in the suppression.  Bands
-//     with an empty mask return before loading anything.  The lists then hold exactly the keypoints of the free
+//     pixel, so that every free pixel still sees the exact responses of its 8 neighbours in the suppression.
+//     lk_fast_plan_kernel (one small CTA per (stream, bin)) builds the mask and lists, per band, the live units of 16
+//     pixel pairs x 1 response row and the bands that have any; lk_fast_band_masked_kernel is a persistent grid over
+//     that work list (no CTA is launched for an empty band, the units are dealt to the half-warps, rows outside the
+//     live range are neither loaded nor searched for maxima).  The lists then hold exactly the keypoints of the free
 //     region (plus possibly false maxima in the one-pixel ring, all of which the selection rejects as too close);
 //     a stream whose selection needs the second-chance pass (:266-304: every keypoint, dist / 2) is flagged by the
 //     selection kernel and redone unmasked by lk_fast_band_flagged_kernel.
@@ -101,7 +104,8 @@ __device__ __forceinline__ uint32_t fb_score_pair(const uint32_t *A, const uint3
 // 640-px frame: every ring tap is then an immediate offset of one base address), 0 = run time (P_rt)
 template <int THREADS, int PC>
 __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restrict__ l0, const LkState &s, uint8_t *__restrict__ score_map,
-					 int bands, int P_rt, int list_cap, size_t stream, int bin, int band, int masked)
+					 int bands, int P_rt, int list_cap, size_t stream, int bin, int band,
+					 const uint16_t *__restrict__ units, uint32_t hdr)
 {
 	const int P = PC ? PC : P_rt;
 	extern __shared__ __align__(16) uint32_t fb_smem[];
@@ -110,8 +114,10 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	uint32_t *sS = sB + FB_PROWS * P;
 	uint32_t *sL = sS + FB_SROWS * P;
 	__shared__ int s_n, s_base;
+	__shared__ uint16_t s_units[FB_SROWS * FB_MWORDS];            // masked: live (response row << 8 | 16-pair segment) units
 
-	if (!score_map && s.bin_needed[stream * LK_BINS + bin] == 0) return;
+	const bool masked = units != nullptr;
+	if (!score_map && !masked && s.bin_needed[stream * LK_BINS + bin] == 0) return;
 	const int W = g.w[0], H = g.h[0], bh = g.bh;
 	const int bw = PC ? (PC - 4) * 2 : g.bw;                      // compile-time bin width: the index arithmetic below folds
 	const int npc = bw >> 1, nq = bw >> 2;
@@ -119,62 +125,13 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	const int y0 = 3 + band * FB_ROWS;                            // first output row of the band (bin coordinates)
 	const int y1 = min(y0 + FB_ROWS, bh - 3);                     // one past the last
 	const int tid = threadIdx.x;
-	// ---- MASKED: which pixels of the band's response rows can matter to the first selection stage
-	__shared__ uint32_t sM[FB_SROWS][FB_MWORDS];
-	__shared__ short2 s_ex[LK_MAX_FEATURES];
-	__shared__ uint16_t s_units[FB_SROWS * FB_MWORDS];            // live (response row << 8 | 16-pair segment) units
-	__shared__ int s_nex, s_nunits, s_rlo, s_rhi;
-	int rlo = 0, rhi = FB_SROWS;                                  // response rows with a live unit (masked only)
+	// masked: the plan's live units of this band; response rows outside [rlo, rhi] hold no live unit.  The responses of
+	// the pairs that are not scored are 0.
+	const int nunits = masked ? (int)(hdr & 0xFFFFu) : 0;
+	const int rlo = masked ? (int)((hdr >> 16) & 0xFFu) : 0, rhi = masked ? (int)(hdr >> 24) : FB_SROWS;
 	if (masked) {
-		const int dist = g.dist, N = g.n_feat;
-		if (tid == 0) { s_nex = 0; s_nunits = 0; s_rlo = FB_SROWS; s_rhi = -1; }
-		__syncthreads();
-		const int npc = s.n_prev_corners[stream];
-		for (int k = tid; k < npc; k += THREADS) {
-			if (!s.prev_status[stream * N + k]) continue;
-			const float2 p = s.prev_corners[stream * N + k];          // int-truncated as in trackFeatures.cpp:212-224
-			const int ex = (int)p.x - c0, ey = (int)p.y - r0;         // bin-local
-			if (ex > -dist && ex < bw - 1 + dist && ey > y0 - 1 - dist && ey < y1 + dist)
-				s_ex[atomicAdd(&s_nex, 1)] = make_short2((short)ex, (short)ey);
-		}
-		__syncthreads();
-		const int nex = s_nex, fmw = (bw + 31) >> 5, rows = y1 - y0 + 2;
-		uint32_t any = 0;
-		for (int i = tid; i < rows * FB_MWORDS; i += THREADS) {
-			const int sr = i / FB_MWORDS, w = i - sr * FB_MWORDS, y = y0 - 1 + sr;
-			uint32_t m = (w < fmw && y >= 3 && y < bh - 3) ? fb_bits(3, bw - 4, 32 * w) : 0u;
-			for (int k = 0; k < nex && m; k++) {
-				const short2 e = s_ex[k];
-				if (abs(e.y - y) < dist - 1) m &= ~fb_bits(e.x - dist + 2, e.x + dist - 2, 32 * w);
-			}
-			sM[sr][w] = m;
-			any |= m;
-		}
-		if (!__syncthreads_or(any != 0)) return;                      // nothing of this band can be accepted
-		// The free part of a bin is a few rectangles: with the static (row group, pair column) mapping below one warp
-		// of a CTA would score all its rows and the others none.  Units of 16 pixel pairs x 1 response row with a mask
-		// bit are listed instead and dealt to the half-warps; the rows outside [rlo, rhi] are neither loaded nor
-		// searched for maxima.  Responses of the pairs that are not scored are 0.
-		const int nseg = ((bw >> 1) + 15) >> 4;
-		const int P_ = PC ? PC : P_rt;
-		uint32_t *zS = fb_smem + 2 * FB_PROWS * P_;
-		for (int i = tid; i < rows * P_; i += THREADS) zS[i] = 0u;
-		const int lo_sr = max(0, 4 - y0), hi_sr = min(rows, bh - 2 - y0);
-		for (int i = tid; i < rows * nseg; i += THREADS) {
-			const int sr = i / nseg, seg = i - sr * nseg;
-			if (sr >= lo_sr && sr < hi_sr && ((sM[sr][seg] >> 1) | (sM[sr][seg + 1] << 31))) {   // pixels 32 seg + 1 .. 32 seg + 32
-				s_units[atomicAdd(&s_nunits, 1)] = (uint16_t)((sr << 8) | seg);
-				atomicMin(&s_rlo, sr);
-				atomicMax(&s_rhi, sr);
-			}
-		}
-		__syncthreads();
-		rlo = s_rlo; rhi = s_rhi;
-		if (tid == 0 && s.lz_stats) { // diagnostics (aof_lk_lazy_stats): band CTAs that scored anything, their live units
-			atomicAdd(&s.lz_stats[0], 1ull);
-			atomicAdd(&s.lz_stats[1], (unsigned long long)s_nunits);
-		}
-		if (rhi < 0) return;                                          // (mask bits only in rows that carry no response)
+		for (int i = tid; i < nunits; i += THREADS) s_units[i] = units[i];
+		for (int i = tid; i < (y1 - y0 + 2) * P; i += THREADS) sS[i] = 0u;
 	}
 	if (tid == 0) s_n = 0;
 	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
@@ -225,8 +182,7 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	const int n_srow = y1 - y0 + 2;
 	const uint32_t lim = (256u + (uint32_t)g.fast_thr) * 0x00010001u;
 	if (masked) {
-		const int half = (tid >> 4) & 1, l16 = tid & 15, nunits = s_nunits;
-		const int jj0 = l16;
+		const int half = (tid >> 4) & 1, jj0 = tid & 15;
 		for (int u = 2 * (tid >> 5) + half; u < nunits; u += 2 * (THREADS / 32)) {
 			const int sr = s_units[u] >> 8, jj = 16 * (s_units[u] & 255) + jj0;
 			if (jj < npc) {
@@ -314,10 +270,96 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 template <int THREADS, int PC>
 __global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
-		    int list_cap, int masked)
+		    int list_cap)
 {
 	const int bin = blockIdx.x / bands;
-	fb_body<THREADS, PC>(g, l0, s, score_map, bands, P_rt, list_cap, blockIdx.y, bin, blockIdx.x - bin * bands, masked);
+	fb_body<THREADS, PC>(g, l0, s, score_map, bands, P_rt, list_cap, blockIdx.y, bin, blockIdx.x - bin * bands, nullptr, 0u);
+}
+
+// MASKED: a persistent grid over the plan's work list (bands with at least one live unit)
+template <int THREADS, int PC>
+__global__ void __launch_bounds__(THREADS, 1280 / THREADS)
+lk_fast_band_masked_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, int bands, int P_rt, int list_cap)
+{
+	const int n_work = s.n_work[0];
+	for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+		const uint32_t item = s.work_list[w];                 // (stream * 16 + bin) * bands + band
+		const uint32_t sb = item / (uint32_t)bands;
+		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)(sb >> 4), (int)(sb & 15u), (int)(item - sb * bands),
+				     s.plan_units + (size_t)item * g.fb_ucap, s.plan_hdr[item]);
+		__syncthreads();                                    // the next item reuses the shared-memory tiles and counters
+	}
+}
+
+// The plan of the masked detector, one CTA per (stream, bin that needs features): the mask of the pixels the first
+// selection stage can accept from (plus one ring pixel for the suppression), then per band the live units and the
+// band's entry in the work list.
+constexpr int FP_THREADS = 128;
+__global__ void __launch_bounds__(FP_THREADS)
+lk_fast_plan_kernel(LkGeom g, LkState s)
+{
+	extern __shared__ __align__(16) uint32_t fp_mask[];           // bh x mw words (mw = mask words per row + 1)
+	__shared__ short2 s_ex[LK_MAX_FEATURES];
+	__shared__ int s_nex;
+	__shared__ int s_cnt[64], s_lo[64], s_hi[64];                 // per band (fb_bands <= 64: lk_fast_band_supported)
+	const size_t stream = blockIdx.y;
+	const int bin = blockIdx.x, tid = threadIdx.x;
+	if (s.bin_needed[stream * LK_BINS + bin] <= 0) return;
+	const int bw = g.bw, bh = g.bh, dist = g.dist, N = g.n_feat, bands = g.fb_bands;
+	const int c0 = (bin >> 2) * bw, r0 = (bin & 3) * bh;
+	const int fmw = (bw + 31) >> 5, mw = fmw + 1, nseg = ((bw >> 1) + 15) >> 4;
+	if (tid == 0) s_nex = 0;
+	if (tid < bands) { s_cnt[tid] = 0; s_lo[tid] = FB_SROWS; s_hi[tid] = -1; }
+	__syncthreads();
+	// active points whose (shrunk) exclusion square reaches into the bin; int-truncated as in trackFeatures.cpp:212-224
+	const int npc = s.n_prev_corners[stream];
+	for (int k = tid; k < npc; k += FP_THREADS) {
+		if (!s.prev_status[stream * N + k]) continue;
+		const float2 p = s.prev_corners[stream * N + k];
+		const int ex = (int)p.x - c0, ey = (int)p.y - r0;         // bin-local
+		if (ex > -dist && ex < bw - 1 + dist && ey > -dist && ey < bh - 1 + dist)
+			s_ex[atomicAdd(&s_nex, 1)] = make_short2((short)ex, (short)ey);
+	}
+	__syncthreads();
+	const int nex = s_nex;
+	// one thread per row: the points whose square covers the row are found once, their column intervals cut out of all
+	// the words of the row
+	for (int y = tid; y < bh; y += FP_THREADS) {
+		uint32_t *row = fp_mask + y * mw;
+		const bool scored = y >= 3 && y < bh - 3;
+		for (int w = 0; w < mw; w++) row[w] = (scored && w < fmw) ? fb_bits(3, bw - 4, 32 * w) : 0u;
+		if (!scored) continue;
+		for (int k = 0; k < nex; k++) {
+			const short2 e = s_ex[k];
+			if (abs(e.y - y) >= dist - 1) continue;
+			const int lo = max(e.x - dist + 2, 0), hi = min(e.x + dist - 2, bw - 1);
+			for (int w = lo >> 5; w <= (hi >> 5); w++) row[w] &= ~fb_bits(lo, hi, 32 * w);
+		}
+	}
+	__syncthreads();
+	// units: band b, response row sr <-> bin row 3 + 38 b - 1 + sr; only rows that carry a response (3 <= y < bh - 3).
+	// One thread per (band, response row).
+	const size_t item0 = (stream * LK_BINS + bin) * (size_t)bands;
+	for (int i = tid; i < bands * FB_SROWS; i += FP_THREADS) {
+		const int b = i / FB_SROWS, sr = i - b * FB_SROWS;
+		const int y0 = 3 + b * FB_ROWS, y1 = min(y0 + FB_ROWS, bh - 3), y = y0 - 1 + sr;
+		if (sr >= y1 - y0 + 2 || y < 3 || y >= bh - 3) continue;
+		const uint32_t *row = fp_mask + y * mw;
+		int live = 0;
+		for (int seg = 0; seg < nseg; seg++)
+			if ((row[seg] >> 1) | (row[seg + 1] << 31)) {                                 // pixels 32 seg + 1 .. 32 seg + 32
+				s.plan_units[(item0 + b) * g.fb_ucap + atomicAdd(&s_cnt[b], 1)] = (uint16_t)((sr << 8) | seg);
+				live = 1;
+			}
+		if (live) { atomicMin(&s_lo[b], sr); atomicMax(&s_hi[b], sr); }
+	}
+	__syncthreads();
+	if (tid < bands && s_cnt[tid] > 0) {
+		s.plan_hdr[item0 + tid] = (uint32_t)s_cnt[tid] | ((uint32_t)s_lo[tid] << 16) | ((uint32_t)s_hi[tid] << 24);
+		s.work_list[atomicAdd(&s.n_work[0], 1)] = (uint32_t)(item0 + tid);
+		atomicAdd(&s.lz_stats[0], 1ull);                          // diagnostics: bands with work, their live units
+		atomicAdd(&s.lz_stats[1], (unsigned long long)s_cnt[tid]);
+	}
 }
 
 // The complete keypoint lists of the FLAGGED streams only (lazy FAST, lk_fast_lazy.cu: the selection kernel lists the
@@ -331,7 +373,7 @@ lk_fast_band_flagged_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s,
 	const int per_stream = LK_BINS * bands;
 	for (int w = blockIdx.x; w < n_flag * per_stream; w += gridDim.x) {
 		const int f = w / per_stream, r = w - f * per_stream, bin = r / bands;
-		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)s.full_list[f], bin, r - bin * bands, 0);
+		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)s.full_list[f], bin, r - bin * bands, nullptr, 0u);
 		__syncthreads();                                    // the next item reuses the shared-memory tiles and counters
 	}
 }
@@ -354,7 +396,7 @@ bool lk_fast_band_supported(const LkGeom &g, const uint8_t *l0)
 }
 
 template <int THREADS, int PC>
-static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked)
+static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
 {
 	int P, cap;
 	const size_t smem = fb_smem_bytes(g, P, cap);
@@ -368,7 +410,7 @@ static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &
 	}
 	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
 	dim3 grid(LK_BINS * bands, n);
-	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap, score_map ? 0 : masked);
+	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
 	return cudaGetLastError();
 }
 
@@ -395,6 +437,56 @@ static cudaError_t fb_launch_flagged(const LkGeom &g, const uint8_t *l0, const L
 	return cudaGetLastError();
 }
 
+template <int THREADS, int PC>
+static cudaError_t fb_launch_masked(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st)
+{
+	int P, cap;
+	const size_t smem = fb_smem_bytes(g, P, cap);
+	static int grid_dev[64] = {};
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev >= 64) return cudaErrorInvalidDevice;
+	if (!grid_dev[dev]) {
+		cudaError_t e = cudaFuncSetAttribute(lk_fast_band_masked_kernel<THREADS, PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+		if (e != cudaSuccess) return e;
+		int sms = 0, per_sm = 0;
+		if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+		if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lk_fast_band_masked_kernel<THREADS, PC>, THREADS, smem)) != cudaSuccess) return e;
+		grid_dev[dev] = sms * (per_sm > 0 ? per_sm : 1);
+	}
+	const long long items = (long long)n * LK_BINS * g.fb_bands;
+	const int grid = (int)(items < grid_dev[dev] ? items : grid_dev[dev]);
+	lk_fast_band_masked_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, g.fb_bands, P, cap);
+	return cudaGetLastError();
+}
+
+static size_t fp_smem_bytes(const LkGeom &g) { return (size_t)g.bh * (((g.bw + 31) >> 5) + 1) * sizeof(uint32_t); }
+
+bool lk_fast_masked_supported(const LkGeom &g, const uint8_t *l0)
+{
+	return lk_fast_band_supported(g, l0) && g.fb_bands <= 64 && fp_smem_bytes(g) <= 48 * 1024 && g.dist >= 2;
+}
+
+// plan (live units per band + work list), then the persistent grid over the bands with work
+cudaError_t lk_fast_masked_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st)
+{
+	if (n <= 0) return cudaSuccess;
+	{
+		KernelTimer kt(KID_LK_FAST_PLAN, st, "lk_fast_plan_kernel");
+		lk_fast_plan_kernel<<<dim3(LK_BINS, n), FP_THREADS, fp_smem_bytes(g), st>>>(g, s);
+		count_launch();
+		cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) return e;
+	}
+	const int npc = g.bw / 2;
+	KernelTimer kt(KID_LK_FAST, st, npc == 80 ? "lk_fast_band_masked_kernel<320,84>" : "lk_fast_band_masked_kernel");
+	count_launch();
+	if (npc == 80) return fb_launch_masked<320, 84>(g, l0, s, n, st);
+	if (4 * npc <= 320) return fb_launch_masked<320, 0>(g, l0, s, n, st);
+	if (4 * npc <= 640) return fb_launch_masked<640, 0>(g, l0, s, n, st);
+	return fb_launch_masked<1024, 0>(g, l0, s, n, st);
+}
+
 cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
@@ -407,15 +499,15 @@ cudaError_t lk_fast_band_flagged_launch(const LkGeom &g, const uint8_t *l0, cons
 	return fb_launch_flagged<1024, 0>(g, l0, s, n, st);
 }
 
-cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked)
+cudaError_t lk_fast_band_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
 {
 	const int npc = g.bw / 2;
 	// 640-px frames: pitch known at compile time.  (640 threads per CTA was measured 24 % slower: 5 rows per thread do
 	// not amortise the per-thread set-up.)
-	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st, masked);
-	if (4 * npc <= 320) return fb_launch<320, 0>(g, l0, s, n, score_map, st, masked);
-	if (4 * npc <= 640) return fb_launch<640, 0>(g, l0, s, n, score_map, st, masked);
-	return fb_launch<1024, 0>(g, l0, s, n, score_map, st, masked);
+	if (npc == 80) return fb_launch<320, 84>(g, l0, s, n, score_map, st);
+	if (4 * npc <= 320) return fb_launch<320, 0>(g, l0, s, n, score_map, st);
+	if (4 * npc <= 640) return fb_launch<640, 0>(g, l0, s, n, score_map, st);
+	return fb_launch<1024, 0>(g, l0, s, n, score_map, st);
 }
 
 } // namespace aof

@@ -702,7 +702,7 @@ lk_fast_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__r
 	}
 }
 
-cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st, int masked)
+cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s, int n, uint8_t *score_map, cudaStream_t st)
 {
 	if (n <= 0) return cudaSuccess;
 	const int tiles_x = (g.bw + FT_TW - 1) / FT_TW, tiles_y = (g.bh + FT_TH - 1) / FT_TH;
@@ -711,7 +711,7 @@ cudaError_t lk_fast_launch(const LkGeom &g, const uint8_t *l0, const LkState &s,
 	KernelTimer kt(KID_LK_FAST, st, !band ? "lk_fast_kernel" : g.bw == 160 ? "lk_fast_band_kernel<320,84>" : "lk_fast_band_kernel");
 	if (band) {
 		count_launch();
-		return lk_fast_band_launch(g, l0, s, n, score_map, st, masked);
+		return lk_fast_band_launch(g, l0, s, n, score_map, st);
 	}
 	if (g.w[0] % 16 == 0 && (reinterpret_cast<uintptr_t>(l0) & 3) == 0)
 		lk_fast_kernel<true><<<grid, FT_THREADS, 0, st>>>(g, l0, s, score_map, tiles_x, tiles_y);
@@ -782,6 +782,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 	const int N = g.n_feat, W = g.w[0];
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	// LK_SEL_FLAGGED: the complete path for the streams the lazy pass flagged, nothing for the others
+	if (mode == LK_SEL_MASKED && blockIdx.x == 0 && tid == 0) s.n_work[0] = 0;   // the masked FAST launch before this one has consumed it
 	if (mode == LK_SEL_FLAGGED) {
 		if (blockIdx.x == 0 && tid == 0) s.n_full[0] = 0;      // the flagged FAST launch before this one has consumed it
 		if (!s.need_full[stream]) return;

@@ -1,7 +1,5 @@
 #!/bin/bash
-# usage: tools/tune_env.sh VAR "v1 v2 ..." [bench args]  -- runs bench.py once per value of VAR and prints the
-# per-kernel event times (tuning aid, not a bench result)
-var=$1; vals=$2; shift 2
-for v in $vals; do
-  env $var=$v python bench.py --no-cpu --steps 30 --warmup 3 "$@" 2>/dev/null | python tools/print_kernels.py "$var=$v"
+# A/B of the LK step under environment switches:  tools/tune_env.sh "AOF_LK_SPLIT=1" "AOF_LK_PARTS=3" ...
+for v in "$@"; do
+  env $v timeout 300 python bench.py --steps 20 --warmup 3 --no-cpu --workload lk 2>/dev/null | python tools/print_kernels.py "[$v]"
 done
