@@ -144,11 +144,22 @@ class ClockSampler:
                 "window": "samples whose nvidia-smi timestamp lies inside the timed region"}
 
 
+def spread_device(local_rank, n_devices):
+    """local rank -> device, alternating between the two halves of the box (0, n/2, 1, n/2 + 1, ...).  On the 8-GPU boxes of
+    this pool the pinned host -> device path is shared per group of four GPUs (profiles/r2_h2d_scaling.json: 52.6 GB/s for
+    one GPU, 2 x 55 for GPUs 0-1, but 4 x 29 for GPUs 0-3; at 8 GPUs 4 x 23.5 + 4 x 35.8): ranks 0..N-1 on devices 0..N-1
+    put all of a 4-rank job behind one group.  Identity when N ranks see N devices."""
+    if n_devices < 4 or n_devices % 2 or local_rank >= n_devices:
+        return local_rank
+    half = n_devices // 2
+    return (local_rank // 2) + (local_rank % 2) * half
+
+
 def dist_setup():
     import torch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    local = spread_device(int(os.environ.get("LOCAL_RANK", "0")), torch.cuda.device_count())
     torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
@@ -870,6 +881,10 @@ def main():
             "warmup": args.warmup, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": p["dtype"], "data": "synthetic", "config": p["config"], "roofline": p["roofline"],
             "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
+    if world > 1:
+        import torch
+        line["config"]["rank_to_device"] = ("local rank r -> device r // 2 + (r % 2) * n / 2 of the n = %d visible devices (spread over the "
+                                            "two host-side groups of the box, profiles/r2_h2d_scaling.json)" % torch.cuda.device_count())
     for key in ("timed_region", "cpu_baseline", "vs_cpu", "single_stream_latency_us", "kernel_rooflines", "fast", "dense", "overlap"):
         if key in p:
             line[key] = p[key]
