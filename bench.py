@@ -815,8 +815,11 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
         "roofline": roof,
         "kernels": kb, "kernel_rooflines": kroof,
         "fast": {"bins_needing_features_frac": bins_frac,
-                 "per_step": {"bins_picked_lazily": lazy[0] / k_steps, "second_collect_passes": lazy[1] / k_steps,
-                              "bins_sent_to_complete_path": lazy[2] / k_steps, "stream_frames_on_complete_path": lazy[3] / k_steps}},
+                 "detector": "masked band FAST (AOF_FAST_LAZY=2): only the pixels the first selection stage can accept from are scored; "
+                             "the int-alu roofline counts the reference's work (every pixel of every bin that needs features)",
+                 "per_step": {"bands_with_work": lazy[0] / k_steps, "live_units_16pairs_x_1row": lazy[1] / k_steps,
+                              "live_unit_frac_of_needed_bins": (lazy[1] / k_steps) / max(1.0, n * 16 * bins_frac * 3 * 40 * 5),
+                              "stream_frames_redone_on_the_complete_path": lazy[3] / k_steps}},
         "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
                 "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
