@@ -19,7 +19,7 @@ def owner_of(stream, total, world):
     return stream // (base + 1) if stream < cut else extra + (stream - cut) // max(base, 1)
 
 
-def gather_results(local, total, world, rank, dist=None):
+def gather_results(local, total, world, rank, dist=None, group=None):
     """host gather: rank 0 receives every rank's structured result array into one array of `total` entries
     (None on the other ranks).  `local` = this rank's results for shard_range(total, world, rank)."""
     local = np.ascontiguousarray(local)
@@ -28,7 +28,7 @@ def gather_results(local, total, world, rank, dist=None):
     if world == 1:
         return local
     parts = [None] * world if rank == 0 else None
-    dist.gather_object(local, parts, dst=0)
+    dist.gather_object(local, parts, dst=0, group=group)   # (bench.py: the gloo host group; the default group there is nccl)
     if rank != 0:
         return None
     out = np.empty(total, local.dtype)

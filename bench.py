@@ -176,17 +176,12 @@ HOST_GROUP = None
 
 def host_gather(res, rank, world):
     """rank 0 receives every rank's result records (16 B per stream) over the host group: the 'host gather' of SURVEY.md
-    8(e).  -> on rank 0 the concatenated records of all ranks, elsewhere None"""
+    8(e) (aero-optical-flow_b200/sharding.py, covered on CPU by tests/test_sharding.py).  -> on rank 0 the records of all
+    ranks in stream order, elsewhere None"""
     if world == 1:
         return res
-    import torch
     import torch.distributed as dist
-    t = torch.from_numpy(np.ascontiguousarray(res).view(np.uint8).reshape(-1))
-    out = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
-    dist.gather(t, out, dst=0, group=HOST_GROUP)
-    if rank != 0:
-        return None
-    return np.concatenate([o.numpy() for o in out]).view(res.dtype)
+    return entry.load_package().sharding.gather_results(res, world * len(res), world, rank, dist, group=HOST_GROUP)
 
 
 def barrier(world):
