@@ -881,8 +881,8 @@ def main():
             "e2e": p["e2e"], "gpu_launches": p["gpu_launches"], "clocks": p["clocks"], "kernels": p["kernels"]}
     if world > 1:
         import torch
-        line["config"]["rank_to_device"] = ("local rank r -> device r // 2 + (r % 2) * n / 2 of the n = %d visible devices (spread over the "
-                                            "two host-side groups of the box, profiles/r2_h2d_scaling.json)" % torch.cuda.device_count())
+        line["config"]["rank_to_device"] = ("local rank r -> device r // 2 + (r mod 2) * n / 2 of the n = {} visible devices (spread over the "
+                                            "two host-side groups of the box, profiles/r2_h2d_scaling.json)").format(torch.cuda.device_count())
     for key in ("timed_region", "cpu_baseline", "vs_cpu", "single_stream_latency_us", "kernel_rooflines", "fast", "dense", "overlap"):
         if key in p:
             line[key] = p[key]
