@@ -38,6 +38,44 @@ def gather_results(local, total, world, rank, dist=None, group=None):
     return out
 
 
+class GatherHandle:
+    """an outstanding host gather (gather_results_async); wait() -> the gathered array on rank 0, None elsewhere"""
+
+    def __init__(self, work, parts, keep, total, world, rank, dtype):
+        self.work, self.parts, self.keep, self.total, self.world, self.rank, self.dtype = work, parts, keep, total, world, rank, dtype
+
+    def wait(self):
+        if self.work is not None:
+            self.work.wait()
+        if self.rank != 0:
+            return None
+        if self.world == 1:
+            return self.keep
+        out = np.empty(self.total, self.dtype)
+        for r, p in enumerate(self.parts):
+            a, b = shard_range(self.total, self.world, r)
+            out[a:b] = p.numpy().view(self.dtype)[: b - a]
+        return out
+
+
+def gather_results_async(local, total, world, rank, dist=None, group=None):
+    """gather_results without blocking: the records travel as bytes (every rank pads its shard to the largest one) on
+    the host group's own thread while the caller runs its next step; call .wait() on the returned handle."""
+    import torch
+    local = np.ascontiguousarray(local)
+    lo, hi = shard_range(total, world, rank)
+    assert len(local) == hi - lo
+    if world == 1:
+        return GatherHandle(None, None, local, total, world, rank, local.dtype)
+    cap = -(-total // world)
+    buf = np.zeros(cap, local.dtype)
+    buf[: hi - lo] = local
+    t = torch.from_numpy(buf.view(np.uint8).reshape(-1))
+    parts = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    work = dist.gather(t, parts, dst=0, group=group, async_op=True)
+    return GatherHandle(work, parts, t, total, world, rank, local.dtype)
+
+
 def max_over_ranks(value, world, dist=None, device="cpu"):
     """max of a per-rank scalar (the benchmark's step time)"""
     if world == 1:

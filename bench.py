@@ -176,12 +176,11 @@ HOST_GROUP = None
 
 def host_gather(res, rank, world):
     """rank 0 receives every rank's result records (16 B per stream) over the host group: the 'host gather' of SURVEY.md
-    8(e) (aero-optical-flow_b200/sharding.py, covered on CPU by tests/test_sharding.py).  -> on rank 0 the records of all
-    ranks in stream order, elsewhere None"""
-    if world == 1:
-        return res
+    8(e) (aero-optical-flow_b200/sharding.py, covered on CPU by tests/test_sharding.py).  Non-blocking: -> a handle whose
+    wait() returns the records of all ranks in stream order on rank 0, None elsewhere."""
     import torch.distributed as dist
-    return entry.load_package().sharding.gather_results(res, world * len(res), world, rank, dist, group=HOST_GROUP)
+    return entry.load_package().sharding.gather_results_async(res, world * len(res), world, rank, dist if world > 1 else None,
+                                                              group=HOST_GROUP)
 
 
 def barrier(world):
@@ -499,18 +498,25 @@ def h2d_probe(keep, world):
     return -max_over_ranks(-best, world)
 
 
-def time_e2e(call, first, steps, world, min_s=MIN_TIMED_S):
-    """host-API steps (synchronous calls: H2D, kernels, D2H inside) between barriers, wall clock, max over ranks; the
-    step count is raised until min_s is timed.  -> (ms total, steps timed, last result)"""
+def time_e2e(call, first, steps, world, rank, min_s=MIN_TIMED_S):
+    """host-API steps (synchronous calls: H2D, kernels, D2H inside) between barriers, wall clock, max over ranks; every
+    step's records are gathered on rank 0 over the host group, one gather in flight while the next step runs, the last
+    one awaited inside the timed region.  The step count is raised until min_s is timed.
+    -> (ms total, steps timed, last gathered result (rank 0) )"""
     import torch
     barrier(world)
-    t0 = time.perf_counter(); res = call(first); probe = time.perf_counter() - t0
+    t0 = time.perf_counter(); res = host_gather(call(first), rank, world).wait(); probe = time.perf_counter() - t0
     probe = max_over_ranks(probe * 1e3, world) * 1e-3
     steps = int(max(steps, min(2000, np.ceil(min_s / max(probe, 1e-6)))))
     barrier(world)
     t0 = time.perf_counter()
+    pending = None
     for k in range(steps):
-        res = call(first + 1 + k)
+        h = host_gather(call(first + 1 + k), rank, world)
+        if pending is not None:
+            res = pending.wait()
+        pending = h
+    res = pending.wait()
     torch.cuda.synchronize()
     return max_over_ranks((time.perf_counter() - t0) * 1e3, world), steps, res
 
@@ -564,8 +570,8 @@ def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False)
     t_us = np.zeros(n, np.uint32)
     for k in range(4):
         flow_e.calc_flow_batch(h_frames[k % rot], t_us + 1000 * k)
-    e2e_ms, e_steps, res = time_e2e(lambda j: host_gather(flow_e.calc_flow_batch(h_frames[(j + 4) % rot], t_us + 1000 * (j + 4)), rank, world),
-                                    0, min(args.steps, 200), world)
+    e2e_ms, e_steps, res = time_e2e(lambda j: flow_e.calc_flow_batch(h_frames[(j + 4) % rot], t_us + 1000 * (j + 4)),
+                                    0, min(args.steps, 200), world, rank)
     if rank == 0:
         assert res.size == world * n and (res["quality"] == 255).mean() > 0.99
     flow_e.close(); flow.close()
@@ -652,7 +658,7 @@ def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False)
         "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": 16 * n, "steps": e_steps,
                 "api": "aof_px4_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
-                       (", then every rank's records gathered on rank 0 over the host (gloo) group" if world > 1 else ""),
+                       (", every step's records gathered on rank 0 over the host (gloo) group, one gather in flight under the next step" if world > 1 else ""),
                 "roofline": {"bound": "pcie-h2d", "achieved": e2e_gbs, "peak": h2d_gbs, "unit": "GB/s per GPU",
                              "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
                              "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},
@@ -723,8 +729,8 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
     t_us = np.zeros(n, np.uint32)
     for j in range(3):
         flow_e.calc_flow_batch(h_frames[j % rot], t_us + 1000 * j)
-    e2e_ms, e_steps, res = time_e2e(lambda j: host_gather(flow_e.calc_flow_batch(h_frames[(j + 3) % rot], t_us + 1000 * (j + 3)), rank, world),
-                                    0, min(args.steps, 30), world)
+    e2e_ms, e_steps, res = time_e2e(lambda j: flow_e.calc_flow_batch(h_frames[(j + 3) % rot], t_us + 1000 * (j + 3)),
+                                    0, min(args.steps, 30), world, rank)
     if rank == 0:
         assert res.size == world * n and (res["quality"] > 60).mean() > 0.97
     flow_e.close()
@@ -818,7 +824,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
         "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
                 "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
-                       (", then every rank's records gathered on rank 0 over the host (gloo) group" if world > 1 else ""),
+                       (", every step's records gathered on rank 0 over the host (gloo) group, one gather in flight under the next step" if world > 1 else ""),
                 "roofline": {"bound": "pcie-h2d", "achieved": e2e_gbs, "peak": h2d_gbs, "unit": "GB/s per GPU",
                              "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
                              "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},

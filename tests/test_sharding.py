@@ -40,6 +40,14 @@ def worker(rank, world, port, q):
     local = run_streams(pkg, lo, hi)
     dist.barrier()
     full = pkg.sharding.gather_results(local, TOTAL, world, rank, dist)
+    # the non-blocking form (bench.py keeps one outstanding while the next step runs): two in flight, same answer
+    h1 = pkg.sharding.gather_results_async(local, TOTAL, world, rank, dist)
+    h2 = pkg.sharding.gather_results_async(local[::-1].copy()[::-1], TOTAL, world, rank, dist)
+    a1, a2 = h1.wait(), h2.wait()
+    if rank == 0:
+        assert np.array_equal(a1, full) and np.array_equal(a2, full)
+    else:
+        assert a1 is None and a2 is None
     slowest = pkg.sharding.max_over_ranks(10.0 + rank, world, dist)
     if rank == 0:
         q.put((full, slowest))
