@@ -521,6 +521,46 @@ def time_e2e(call, first, steps, world, rank, min_s=MIN_TIMED_S):
     return max_over_ranks((time.perf_counter() - t0) * 1e3, world), steps, res
 
 
+def host_threaded_leg(make, frames, n, world, rank, min_s=MIN_TIMED_S):
+    """The same end-to-end workload through the library's own multi-GPU entry points (aof_*_create_multi: ONE process, one
+    host worker thread per device, every device's D2H landing in one pinned result array = the host gather, no torch and no
+    collective).  Rank 0 drives all `world` devices while the other ranks wait at a barrier.  -> dict or None"""
+    import torch
+    if world == 1:
+        return None
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    dist.barrier(group=HOST_GROUP)          # host-side: the waiting ranks must not spin in a kernel on the GPUs rank 0 is about to use
+    out = None
+    if rank == 0:
+        devices = [spread_device(r, torch.cuda.device_count()) for r in range(world)]
+        rot = min(2, frames.shape[0])
+        per = frames[0].size // n                                        # bytes per frame
+        keep = torch.empty((rot, world * n, per), dtype=torch.uint8, pin_memory=True)
+        host = keep.numpy()
+        for k in range(rot):
+            for d in range(world):
+                host[k, d * n:(d + 1) * n] = frames[k].reshape(n, per)
+        m = make(world * n, devices)
+        t_us = np.zeros(world * n, np.uint32)
+        for k in range(3):
+            m.calc_flow_batch(host[k % rot], t_us + 1000 * k, copy=False)
+        t0 = time.perf_counter(); m.calc_flow_batch(host[1 % rot], t_us + 3000, copy=False); probe = time.perf_counter() - t0
+        steps = int(max(3, min(2000, np.ceil(min_s / max(probe, 1e-6)))))
+        t0 = time.perf_counter()
+        for k in range(steps):
+            res = m.calc_flow_batch(host[k % rot], t_us + 1000 * (k + 4), copy=False)
+        dt = time.perf_counter() - t0
+        assert res.size == world * n and (res["quality"] > 60).mean() > 0.97
+        out = {"value": world * n * steps / dt, "unit": "frame-pairs/s", "steps": steps, "devices": devices, "ranges": m.ranges(),
+               "api": "aof_*_create_multi + aof_*_multi_calc_flow_batch: one process, a host worker thread per device, results in the "
+                      "library's one pinned array (host gather inside the call)"}
+        m.close()
+        del keep
+    dist.barrier(group=HOST_GROUP)
+    return out
+
+
 def find_kernel(kb, prefix):
     """the entry of the timing table whose kernel symbol starts with `prefix` (the table names what actually ran)"""
     for name in kb:
@@ -576,6 +616,9 @@ def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False)
         assert res.size == world * n and (res["quality"] == 255).mean() > 0.99
     flow_e.close(); flow.close()
     h2d_gbs = h2d_probe(keep, world)
+    multi = None if light else host_threaded_leg(
+        lambda total, devs: pkg.Px4FlowMulti(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=total, devices=devs),
+        h_frames, n, world, rank)
 
     # BASELINE config 1 as written: ONE 64x64 stream, host frame in, result out (latency, not throughput)
     lat_us = None
@@ -665,6 +708,8 @@ def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False)
         "gpu_launches": int(launches), "clocks": clocks, "dtype": "u8",
     }
     r["single_stream_latency_us"] = lat_us
+    if multi is not None:
+        r["e2e_host_threaded"] = multi
     if dense is not None:
         if "alu_packed_instr_per_s" in pk:
             a = dense["blocks_per_pair"] * 4944.0 * dense["pairs_per_s"]     # 289 x 16 SAD + 320 sub-pixel instr per block
@@ -735,6 +780,9 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
         assert res.size == world * n and (res["quality"] > 60).mean() > 0.97
     flow_e.close()
     h2d_gbs = h2d_probe(keep, world)
+    multi = host_threaded_leg(
+        lambda total, devs: pkg.LkFlowMulti(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=total, devices=devs),
+        h_frames, n, world, rank)
 
     # single-stream latency (BASELINE config 2 as written: one stream, host frame in, result out)
     one = pkg.LkFlow(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=1, device=local)
@@ -829,6 +877,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
                              "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
                              "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},
         "single_stream_latency_us": lat_us,
+        "e2e_host_threaded": multi,
         "overlap": "value: the device entry point pipelines two halves of the streams over two CUDA streams (the latency-bound "
                    "kernels of one half under the throughput kernels of the other); kernels / kernel_rooflines: the same steps with "
                    "per-kernel event timing on, which runs them unsplit, each kernel alone on the GPU (what a burst roofline "
@@ -889,7 +938,7 @@ def main():
         import torch
         line["config"]["rank_to_device"] = ("local rank r -> device r // 2 + (r mod 2) * n / 2 of the n = {} visible devices (spread over the "
                                             "two host-side groups of the box, profiles/r2_h2d_scaling.json)").format(torch.cuda.device_count())
-    for key in ("timed_region", "cpu_baseline", "vs_cpu", "single_stream_latency_us", "kernel_rooflines", "fast", "dense", "overlap"):
+    for key in ("timed_region", "cpu_baseline", "vs_cpu", "single_stream_latency_us", "e2e_host_threaded", "kernel_rooflines", "fast", "dense", "overlap"):
         if key in p:
             line[key] = p[key]
     if args.workload == "both":
