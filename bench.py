@@ -673,7 +673,7 @@ def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False)
     hbm = n * SAD_BYTES_PER_PAIR / (kern_ms * 1e-3) / 1e9
     hbm_obj = {"bound": "hbm", "achieved": hbm, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": hbm / pk["hbm_gbs"],
                "peak_source": pk["which"], "algorithmic_bytes_per_launch": n * SAD_BYTES_PER_PAIR,
-               "traffic": ncu_traffic("sad_flow_kernel", n, 4096)}
+               "traffic": ncu_traffic(kname.split("<")[0], n, 4096)}
     if "alu_packed_instr_per_s" in pk:
         # the binding roofline: 40 550 packed-byte SAD instructions per pair against the measured
         # VABSDIFF4 issue rate of the ALU pipe (profiles/alu_peak.json, tools/ubench.cu)

@@ -9,9 +9,9 @@ python bench.py > $O/${T}_bench.json 2> $O/${T}_bench.err; echo "bench exit $?"
 python bench.py --impl reference --steps 2 --warmup 1 > $O/${T}_bench_ref.json 2>&1; echo "ref exit $?"
 python bench.py --steps 3 --warmup 3 --no-cpu > $O/${T}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${T}_launches.csv python bench.py --steps 3 --warmup 3 --no-cpu > $O/${T}_ncu1.log 2>&1
-# full capture of the UNSPLIT kernels (the ones kernel_rooflines times): AOF_LK_SPLIT=1
-AOF_LK_SPLIT=1 python bench.py --steps 3 --warmup 3 --no-cpu --workload lk > $O/${T}_plain2.log 2>&1 &&
-AOF_LK_SPLIT=1 ncu --set full --clock-control none --import-source on -k regex:lk_ -s 12 -c 8 -o $O/${T}_lk_full python bench.py --steps 3 --warmup 3 --no-cpu --workload lk > $O/${T}_ncu2.log 2>&1
+# full capture of two steady-state LK steps (7 launches each: pyramid, track, plan, masked band, select, flagged band, select)
+python bench.py --steps 3 --warmup 3 --no-cpu --workload lk > $O/${T}_plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:lk_ -s 21 -c 14 -o $O/${T}_lk_full -f python bench.py --steps 3 --warmup 3 --no-cpu --workload lk > $O/${T}_ncu2.log 2>&1
 python bench.py --steps 3 --warmup 3 --no-cpu --workload sad > $O/${T}_plain3.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:sad_flow -s 5 -c 2 -o $O/${T}_sad_full python bench.py --steps 3 --warmup 3 --no-cpu --workload sad > $O/${T}_ncu3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:sad_flow -s 5 -c 2 -o $O/${T}_sad_full -f python bench.py --steps 3 --warmup 3 --no-cpu --workload sad > $O/${T}_ncu3.log 2>&1
 ls -la $O | grep ${T}_
