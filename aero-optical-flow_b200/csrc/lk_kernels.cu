@@ -455,11 +455,14 @@ lk_track_update_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_pre
 // an LK point is a long chain of dependent gathers (up to 4 levels x 30 iterations), so the time of the CTA-per-stream
 // form is the time of the warp that drew the three slowest points.  Here every point is its own warp, the CTAs of all
 // streams share the SMs dynamically, and the LAST CTA of a stream to finish (ticket counter) does the bookkeeping.
+// Measured (r2B, 512 streams x 20 features, B200): CTAs of 4 point-warps at 8 per SM 104.4 us, 2 at 16 103.0, ONE warp per
+// CTA at 32 per SM 95.7 us (at 24 per SM, 72 registers: 99.3): a finished warp no longer holds its CTA's slots while the
+// slowest point of the CTA runs on (27 % of the stall samples of the 4-warp form sat at its closing barrier).
 #ifndef AOF_TS_WARPS
-#define AOF_TS_WARPS 4
+#define AOF_TS_WARPS 1
 #endif
 #ifndef AOF_TS_MINB
-#define AOF_TS_MINB 8
+#define AOF_TS_MINB 32
 #endif
 constexpr int TS_WARPS = AOF_TS_WARPS;
 
@@ -468,7 +471,7 @@ lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev
 {
 	__shared__ LkWarpScratch s_sc[TS_WARPS];
 	__shared__ int s_per_bin[LK_BINS];
-	__shared__ int s_last;
+	__shared__ int s_last, s_target;
 	const int stream_i = blockIdx.x / groups, grp = blockIdx.x - stream_i * groups;
 	const size_t stream = stream_i;
 	const int N = g.n_feat;
@@ -497,12 +500,13 @@ lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev
 		__threadfence();
 		s_last = atomicAdd(&s.ticket[stream], 1) == groups - 1;
 	}
-	if (threadIdx.x < LK_BINS) s_per_bin[threadIdx.x] = 0;
+	for (int b = threadIdx.x; b < LK_BINS; b += blockDim.x) s_per_bin[b] = 0;
+	if (threadIdx.x == 0) s_target = 0;
 	__syncthreads();
 	if (!s_last) return;
 	__threadfence();
 	if (threadIdx.x == 0) s.ticket[stream] = 0;
-	if (threadIdx.x < LK_BINS) s.kp_count[stream * LK_BINS + threadIdx.x] = 0;
+	for (int b = threadIdx.x; b < LK_BINS; b += blockDim.x) s.kp_count[stream * LK_BINS + b] = 0;
 	// trackFeatures.cpp:77-125, one thread per slot; then the demand of initMorePoints (:144-183): bin = x * 4 + y
 	int wants = 0;
 	for (int i = threadIdx.x; i < N; i += blockDim.x) {
@@ -530,9 +534,11 @@ lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev
 			if (bx < 4 && by < 4) atomicAdd(&s_per_bin[bx * 4 + by], 1);
 		}
 	}
-	const int target = __syncthreads_count(wants); // N <= blockDim.x: at most one slot per thread
-	if (threadIdx.x < LK_BINS)
-		s.bin_needed[stream * LK_BINS + threadIdx.x] = target ? max(0, g.tpb - s_per_bin[threadIdx.x]) : 0;
+	if (wants) atomicAdd(&s_target, wants);            // (a thread may own several slots when the CTA is narrower than N)
+	__syncthreads();
+	const int target = s_target;
+	for (int b = threadIdx.x; b < LK_BINS; b += blockDim.x)
+		s.bin_needed[stream * LK_BINS + b] = target ? max(0, g.tpb - s_per_bin[b]) : 0;
 	if (threadIdx.x == 0) s.target[stream] = target;
 }
 
