@@ -21,6 +21,11 @@ namespace aof {
 #define DENSE_MINB 5   // CTAs per SM (40 registers, no spill).  Measured on B200, 1280x720 +-8: 8x4-block CTAs at 2 / 3 per SM
                        // 105 k / 127 k pairs/s, 8x2-block CTAs at 5 per SM 133 k: more, smaller CTAs overlap their phases better
 #endif
+#ifndef DENSE_FMA
+#define DENSE_FMA 0   // 1 = byte alignment of the window rows on the FMA pipe.  Measured (r2D, 1280x720 +-8): 112.7 k pairs/s against
+                      // 133.1 k with funnel shifts, although the ALU pipe is 84 % busy: IMAD.HI issues at half rate and the four
+                      // extra instructions per row cost more issue slots than the two ALU slots they free
+#endif
 constexpr int DN_BX = 8, DN_BY = 2, DN_BLOCKS = DN_BX * DN_BY;
 constexpr int DN_MARGIN = 12;                       // columns left of the tile in smem (>= S + 1, multiple of 4)
 constexpr int DN_CP = DN_BX * 8 + 2 * DN_MARGIN;    // pitch of the current-frame tile: 88 bytes
@@ -113,11 +118,26 @@ sad_dense_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 			// window column of displacement ii: tile column (b & 7) * 8 + MARGIN - S + ii; first row: block row * 8 + 1
 			const uint32_t off = (uint32_t)((b >> 3) * 8 + 1) * DN_CP + (b & 7) * 8 + DN_MARGIN - S + ii;
 			const uint32_t sh8 = (off & 3u) * 8;
+#if DENSE_FMA
+			// byte alignment on the FMA pipe: bytes [k, k + 4) of w0:w1 = hi32(w0 * 2^(32 - 8k)) + lo32(w1 * 2^(32 - 8k)); k = 0 is
+			// the same formula one word earlier with the multiplier 2^0 (A/B only, see DENSE_FMA)
+			const uint32_t m = sh8 ? 1u << (32u - sh8) : 1u;
+			const uint32_t *w = reinterpret_cast<const uint32_t *>(s_cur + (off & ~3u)) - (sh8 ? 0 : 1);
+#else
 			const uint32_t *w = reinterpret_cast<const uint32_t *>(s_cur + (off & ~3u));
+#endif
 #pragma unroll
 			for (int r = 0; r < Cfg::ROWS; r++) {
 				const uint32_t w0 = w[r * (DN_CP / 4)], w1 = w[r * (DN_CP / 4) + 1], w2 = w[r * (DN_CP / 4) + 2];
+#if DENSE_FMA
+				uint32_t c0, c1, l0, l1;
+				asm("mul.lo.u32 %0, %1, %2;" : "=r"(l0) : "r"(w1), "r"(m));
+				asm("mul.lo.u32 %0, %1, %2;" : "=r"(l1) : "r"(w2), "r"(m));
+				asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(c0) : "r"(w0), "r"(m), "r"(l0));
+				asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(c1) : "r"(w1), "r"(m), "r"(l1));
+#else
 				const uint32_t c0 = __funnelshift_r(w0, w1, sh8), c1 = __funnelshift_r(w1, w2, sh8);
+#endif
 #pragma unroll
 				for (int q = 0; q < NI; q++) {
 					const int br = r - q;
