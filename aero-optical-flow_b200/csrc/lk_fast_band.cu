@@ -127,20 +127,11 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	const int tid = threadIdx.x;
 	// masked: the plan's live units of this band; response rows outside [rlo, rhi] hold no live unit.  The responses of
 	// the pairs that are not scored are 0.
-	// hdr = units (10 bits) | first / last live response row (6 + 6) | first / last live segment (5 + 5): everything below
-	// works on that bounding box only (on the LK benchmark it covers 52 % of a band that has work, its rows alone 87 %)
-	const int nunits = masked ? (int)(hdr & 1023u) : 0;
-	const int rlo = masked ? (int)((hdr >> 10) & 63u) : 0, rhi = masked ? (int)((hdr >> 16) & 63u) : FB_SROWS;
-	const int ja = masked ? 16 * (int)((hdr >> 22) & 31u) : 0;                    // scored pair columns [ja, jb]
-	const int jb = masked ? min(16 * (int)(hdr >> 27) + 15, npc - 1) : npc - 1;
+	const int nunits = masked ? (int)(hdr & 0xFFFFu) : 0;
+	const int rlo = masked ? (int)((hdr >> 16) & 0xFFu) : 0, rhi = masked ? (int)(hdr >> 24) : FB_SROWS;
 	if (masked) {
 		for (int i = tid; i < nunits; i += THREADS) s_units[i] = units[i];
-		// the responses the suppression of the box reads: rows rlo - 1 .. rhi + 1, pair columns ja - 1 .. jb + 1
-		const int z0 = max(rlo - 1, 0), z1 = min(rhi + 2, y1 - y0 + 2), c0z = max(ja - 1, 0), wz = min(jb + 1, P - 1) - c0z + 1;
-		for (int i = tid; i < (z1 - z0) * wz; i += THREADS) {
-			const int r = i / wz;
-			sS[(z0 + r) * P + c0z + (i - r * wz)] = 0u;
-		}
+		for (int i = tid; i < (y1 - y0 + 2) * P; i += THREADS) sS[i] = 0u;
 	}
 	if (tid == 0) s_n = 0;
 	const uint8_t *img = l0 + stream * (size_t)W * H + (size_t)r0 * W + c0;
@@ -158,31 +149,11 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 		int tt[LD_ROUNDS], qq[LD_ROUNDS];
 		const uint32_t *img32 = reinterpret_cast<const uint32_t *>(img);
 		const int W4 = W >> 2;
-		if (masked) {
-			// tile rows rlo .. rhi + 6 (response row sr reads tile rows sr .. sr + 6), words of the pair columns ja - 1 .. jb + 2
-			const int tlo = rlo, nrow = min(rhi + 6, n_prow - 1) - tlo + 1;
-			const int qlo = max(ja - 1, 0) >> 1, wq = min((jb + 2) >> 1, nq - 1) - qlo + 1;
-			const int total = nrow * wq;
-			const uint32_t rcp = (uint32_t)((0x100000000ull + (unsigned)wq - 1) / (unsigned)wq);
-#pragma unroll
-			for (int k = 0; k < LD_ROUNDS; k++) {
-				tt[k] = -1; qq[k] = 0; w0[k] = w1[k] = 0u;
-				if (k * THREADS >= total) continue;                   // uniform: whole rounds fall away with a small box
-				const int i = tid + k * THREADS;
-				const int r = (int)__umulhi((uint32_t)i, rcp), tk = tlo + r, qk = qlo + (i - r * wq), y = y0 - 4 + tk;
-				if (i < total && y >= 0 && y < bh) {
-					tt[k] = tk; qq[k] = qk;
-					const uint32_t *row = img32 + y * W4;
-					w0[k] = __ldg(row + qk);
-					w1[k] = __ldg(row + (qk + 1 < nq ? qk + 1 : qk));
-				}
-			}
-		} else
 #pragma unroll
 		for (int k = 0; k < LD_ROUNDS; k++) {
 			const int y = y0 - 4 + t;
-			// rows -1 and bh only feed responses that are not computed
-			const bool on = t < n_prow && y >= 0 && y < bh;
+			// rows -1 and bh only feed responses that are not computed; masked: response row sr reads tile rows sr .. sr + 6
+			const bool on = t < n_prow && y >= 0 && y < bh && t >= rlo && t <= rhi + 6;
 			tt[k] = on ? t : -1; qq[k] = q;
 			const uint32_t *row = img32 + (on ? y * W4 : 0);      // 32-bit offsets: a bin is far below 2^31 bytes
 			w0[k] = __ldg(row + q);
@@ -234,26 +205,12 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	}
 	__syncthreads();
 
-	// ---- 3 x 3 non-maximum suppression, each thread walking down its share of the band's rows (masked: of the box's rows,
-	// the threads spread over the box's columns only)
-	const int n_out = y1 - y0;
-	const int oa = max(1, rlo), ob = min(n_out + 1, rhi + 1);
-	int n_j = j, n_grp = grp, n_ngrp = ngrp;
-	bool n_ok = col_ok;
-	if (masked) {
-		const int j0 = max(ja, 1), wj = min(jb, npc - 3) - j0 + 1;
-		n_ok = false;
-		if (wj > 0 && ob > oa) {
-			n_ngrp = max(1, min(THREADS / wj, (ob - oa + 3) / 4));          // at least 4 rows per walk: its set-up is two rows
-			n_grp = tid / wj;
-			n_j = j0 + (tid - n_grp * wj);
-			n_ok = n_grp < n_ngrp;
-		}
-	}
-	if (n_ok) {
-		const int chunk = (max(ob - oa, 0) + n_ngrp - 1) / n_ngrp;
-		const int ra = oa + n_grp * chunk, rb = min(ra + chunk, ob);       // response rows of this thread's outputs
-		const int j = n_j;
+	// ---- 3 x 3 non-maximum suppression, each thread walking down its share of the band's rows
+	if (col_ok) {
+		const int n_out = y1 - y0;
+		const int oa = max(1, rlo), ob = min(n_out + 1, rhi + 1);          // (masked: the rows with a live unit only)
+		const int chunk = (max(ob - oa, 0) + ngrp - 1) / ngrp;
+		const int ra = oa + grp * chunk, rb = min(ra + chunk, ob);         // response rows of this thread's outputs
 		const uint32_t *col = sS + j;
 		auto hmax = [&](int sr, uint32_t &c, uint32_t &side) -> uint32_t {
 			const uint32_t l = col[sr * P - 1], r = col[sr * P + 1];
@@ -344,7 +301,7 @@ lk_fast_plan_kernel(LkGeom g, LkState s)
 	extern __shared__ __align__(16) uint32_t fp_mask[];           // bh x mw words (mw = mask words per row + 1)
 	__shared__ short2 s_ex[LK_MAX_FEATURES];
 	__shared__ int s_nex;
-	__shared__ int s_cnt[64], s_lo[64], s_hi[64], s_clo[64], s_chi[64];   // per band (fb_bands <= 64: lk_fast_masked_supported)
+	__shared__ int s_cnt[64], s_lo[64], s_hi[64];                 // per band (fb_bands <= 64: lk_fast_band_supported)
 	const size_t stream = blockIdx.y;
 	const int bin = blockIdx.x, tid = threadIdx.x;
 	if (s.bin_needed[stream * LK_BINS + bin] <= 0) return;
@@ -352,7 +309,7 @@ lk_fast_plan_kernel(LkGeom g, LkState s)
 	const int c0 = (bin >> 2) * bw, r0 = (bin & 3) * bh;
 	const int fmw = (bw + 31) >> 5, mw = fmw + 1, nseg = ((bw >> 1) + 15) >> 4;
 	if (tid == 0) s_nex = 0;
-	if (tid < bands) { s_cnt[tid] = 0; s_lo[tid] = FB_SROWS; s_hi[tid] = -1; s_clo[tid] = 31; s_chi[tid] = 0; }
+	if (tid < bands) { s_cnt[tid] = 0; s_lo[tid] = FB_SROWS; s_hi[tid] = -1; }
 	__syncthreads();
 	// active points whose (shrunk) exclusion square reaches into the bin; int-truncated as in trackFeatures.cpp:212-224
 	const int npc = s.n_prev_corners[stream];
@@ -392,15 +349,13 @@ lk_fast_plan_kernel(LkGeom g, LkState s)
 		for (int seg = 0; seg < nseg; seg++)
 			if ((row[seg] >> 1) | (row[seg + 1] << 31)) {                                 // pixels 32 seg + 1 .. 32 seg + 32
 				s.plan_units[(item0 + b) * g.fb_ucap + atomicAdd(&s_cnt[b], 1)] = (uint16_t)((sr << 8) | seg);
-				if (!live) atomicMin(&s_clo[b], seg);                         // (segments ascend: the first live one is the row's minimum)
-				live = seg + 1;
+				live = 1;
 			}
-		if (live) { atomicMin(&s_lo[b], sr); atomicMax(&s_hi[b], sr); atomicMax(&s_chi[b], live - 1); }
+		if (live) { atomicMin(&s_lo[b], sr); atomicMax(&s_hi[b], sr); }
 	}
 	__syncthreads();
 	if (tid < bands && s_cnt[tid] > 0) {
-		s.plan_hdr[item0 + tid] = (uint32_t)s_cnt[tid] | ((uint32_t)s_lo[tid] << 10) | ((uint32_t)s_hi[tid] << 16) |
-					  ((uint32_t)s_clo[tid] << 22) | ((uint32_t)s_chi[tid] << 27);
+		s.plan_hdr[item0 + tid] = (uint32_t)s_cnt[tid] | ((uint32_t)s_lo[tid] << 16) | ((uint32_t)s_hi[tid] << 24);
 		s.work_list[atomicAdd(&s.n_work[0], 1)] = (uint32_t)(item0 + tid);
 		atomicAdd(&s.lz_stats[0], 1ull);                          // diagnostics: bands with work, their live units
 		atomicAdd(&s.lz_stats[1], (unsigned long long)s_cnt[tid]);
