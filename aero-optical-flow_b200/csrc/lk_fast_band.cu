@@ -282,12 +282,20 @@ __global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_masked_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, int bands, int P_rt, int list_cap)
 {
 	const int n_work = s.n_work[0];
-	for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
-		const uint32_t item = s.work_list[w];                 // (stream * 16 + bin) * bands + band
+	int w = blockIdx.x;
+	// the item and its header are two dependent global round trips: those of the NEXT item are issued before this item's
+	// work and land while it runs
+	uint32_t item = w < n_work ? s.work_list[w] : 0u;          // (stream * 16 + bin) * bands + band
+	uint32_t hdr = w < n_work ? s.plan_hdr[item] : 0u;
+	for (; w < n_work; w += gridDim.x) {
+		const int wn = w + (int)gridDim.x;
+		uint32_t item_n = 0u, hdr_n = 0u;
+		if (wn < n_work) { item_n = s.work_list[wn]; hdr_n = s.plan_hdr[item_n]; }
 		const uint32_t sb = item / (uint32_t)bands;
 		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)(sb >> 4), (int)(sb & 15u), (int)(item - sb * bands),
-				     s.plan_units + (size_t)item * g.fb_ucap, s.plan_hdr[item]);
+				     s.plan_units + (size_t)item * g.fb_ucap, hdr);
 		__syncthreads();                                    // the next item reuses the shared-memory tiles and counters
+		item = item_n; hdr = hdr_n;
 	}
 }
 
@@ -304,24 +312,69 @@ lk_fast_plan_kernel(LkGeom g, LkState s)
 	__shared__ int s_cnt[64], s_lo[64], s_hi[64];                 // per band (fb_bands <= 64: lk_fast_band_supported)
 	const size_t stream = blockIdx.y;
 	const int bin = blockIdx.x, tid = threadIdx.x;
-	if (s.bin_needed[stream * LK_BINS + bin] <= 0) return;
 	const int bw = g.bw, bh = g.bh, dist = g.dist, N = g.n_feat, bands = g.fb_bands;
+	// everything the CTA reads from global memory is requested at once (one round trip instead of a chain of four)
+	const int needed = s.bin_needed[stream * LK_BINS + bin];
+	const int npc = s.n_prev_corners[stream];
+	uint8_t st0 = 0;
+	float2 p0 = make_float2(0.f, 0.f);
+	if (tid < N) { st0 = s.prev_status[stream * N + tid]; p0 = s.prev_corners[stream * N + tid]; }
+	if (needed <= 0) return;
 	const int c0 = (bin >> 2) * bw, r0 = (bin & 3) * bh;
 	const int fmw = (bw + 31) >> 5, mw = fmw + 1, nseg = ((bw >> 1) + 15) >> 4;
 	if (tid == 0) s_nex = 0;
 	if (tid < bands) { s_cnt[tid] = 0; s_lo[tid] = FB_SROWS; s_hi[tid] = -1; }
 	__syncthreads();
 	// active points whose (shrunk) exclusion square reaches into the bin; int-truncated as in trackFeatures.cpp:212-224
-	const int npc = s.n_prev_corners[stream];
-	for (int k = tid; k < npc; k += FP_THREADS) {
-		if (!s.prev_status[stream * N + k]) continue;
-		const float2 p = s.prev_corners[stream * N + k];
+	for (int k = tid; k < npc; k += FP_THREADS) {                 // (N <= LK_MAX_FEATURES <= FP_THREADS: one slot per thread, held above)
+		const uint8_t st = k == tid ? st0 : s.prev_status[stream * N + k];
+		if (!st) continue;
+		const float2 p = k == tid ? p0 : s.prev_corners[stream * N + k];
 		const int ex = (int)p.x - c0, ey = (int)p.y - r0;         // bin-local
 		if (ex > -dist && ex < bw - 1 + dist && ey > -dist && ey < bh - 1 + dist)
 			s_ex[atomicAdd(&s_nex, 1)] = make_short2((short)ex, (short)ey);
 	}
 	__syncthreads();
 	const int nex = s_nex;
+	const size_t item0 = (stream * LK_BINS + bin) * (size_t)bands;
+	if (fmw <= 8) {
+		// bins up to 256 px wide: the column interval of every point as 8 mask words (once per point), then one thread per
+		// row ANDs the words of the points whose square covers the row in registers and emits the row's live units for
+		// the one or two bands the row belongs to -- no mask array, no second pass
+		uint32_t *xm = fp_mask;                                   // [nex][8]
+		for (int i = tid; i < nex * 8; i += FP_THREADS) {
+			const short2 e = s_ex[i >> 3];
+			xm[i] = ~fb_bits(max(e.x - dist + 2, 0), min(e.x + dist - 2, bw - 1), 32 * (i & 7));
+		}
+		__syncthreads();
+		for (int y = 3 + tid; y < bh - 3; y += FP_THREADS) {
+			uint32_t m[9];
+#pragma unroll
+			for (int w = 0; w < 8; w++) m[w] = w < fmw ? fb_bits(3, bw - 4, 32 * w) : 0u;
+			m[8] = 0u;
+			for (int k = 0; k < nex; k++) {
+				if (abs(s_ex[k].y - y) >= dist - 1) continue;
+				const uint4 lo4 = *reinterpret_cast<const uint4 *>(xm + 8 * k), hi4 = *reinterpret_cast<const uint4 *>(xm + 8 * k + 4);
+				m[0] &= lo4.x; m[1] &= lo4.y; m[2] &= lo4.z; m[3] &= lo4.w;
+				m[4] &= hi4.x; m[5] &= hi4.y; m[6] &= hi4.z; m[7] &= hi4.w;
+			}
+			uint32_t live = 0;
+#pragma unroll
+			for (int seg = 0; seg < 8; seg++)
+				if (seg < nseg && ((m[seg] >> 1) | (m[seg + 1] << 31))) live |= 1u << seg;    // pixels 32 seg + 1 .. 32 seg + 32
+			if (!live) continue;
+			// row y is response row y - (3 + 38 b - 1) of band b; rows at a band seam belong to both neighbours
+			const int b_hi = min((y - 2) / FB_ROWS, bands - 1);
+			for (int bnd = max(b_hi - 1, 0); bnd <= b_hi; bnd++) {
+				const int y0 = 3 + bnd * FB_ROWS, y1 = min(y0 + FB_ROWS, bh - 3), sr = y - (y0 - 1);
+				if (sr < 0 || sr >= y1 - y0 + 2) continue;
+				uint16_t *out = s.plan_units + (item0 + bnd) * g.fb_ucap + atomicAdd(&s_cnt[bnd], __popc(live));
+				for (uint32_t l = live; l; l &= l - 1u) *out++ = (uint16_t)((sr << 8) | (__ffs((int)l) - 1));
+				atomicMin(&s_lo[bnd], sr);
+				atomicMax(&s_hi[bnd], sr);
+			}
+		}
+	} else {
 	// one thread per row: the points whose square covers the row are found once, their column intervals cut out of all
 	// the words of the row
 	for (int y = tid; y < bh; y += FP_THREADS) {
@@ -339,7 +392,6 @@ lk_fast_plan_kernel(LkGeom g, LkState s)
 	__syncthreads();
 	// units: band b, response row sr <-> bin row 3 + 38 b - 1 + sr; only rows that carry a response (3 <= y < bh - 3).
 	// One thread per (band, response row).
-	const size_t item0 = (stream * LK_BINS + bin) * (size_t)bands;
 	for (int i = tid; i < bands * FB_SROWS; i += FP_THREADS) {
 		const int b = i / FB_SROWS, sr = i - b * FB_SROWS;
 		const int y0 = 3 + b * FB_ROWS, y1 = min(y0 + FB_ROWS, bh - 3), y = y0 - 1 + sr;
@@ -352,6 +404,7 @@ lk_fast_plan_kernel(LkGeom g, LkState s)
 				live = 1;
 			}
 		if (live) { atomicMin(&s_lo[b], sr); atomicMax(&s_hi[b], sr); }
+	}
 	}
 	__syncthreads();
 	if (tid < bands && s_cnt[tid] > 0) {
@@ -460,7 +513,11 @@ static cudaError_t fb_launch_masked(const LkGeom &g, const uint8_t *l0, const Lk
 	return cudaGetLastError();
 }
 
-static size_t fp_smem_bytes(const LkGeom &g) { return (size_t)g.bh * (((g.bw + 31) >> 5) + 1) * sizeof(uint32_t); }
+static size_t fp_smem_bytes(const LkGeom &g)
+{
+	const size_t rows = (size_t)g.bh * (((g.bw + 31) >> 5) + 1), pts = (size_t)LK_MAX_FEATURES * 8;   // mask rows / per-point words
+	return (rows > pts ? rows : pts) * sizeof(uint32_t);
+}
 
 bool lk_fast_masked_supported(const LkGeom &g, const uint8_t *l0)
 {
