@@ -113,7 +113,7 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	uint32_t *sB = sA + FB_PROWS * P;
 	uint32_t *sS = sB + FB_PROWS * P;
 	uint32_t *sL = sS + FB_SROWS * P;
-	__shared__ int s_n, s_base;
+	__shared__ int s_n;
 	__shared__ uint16_t s_units[FB_SROWS * FB_MWORDS];            // masked: live (response row << 8 | 16-pair segment) units
 
 	const bool masked = units != nullptr;
@@ -255,14 +255,20 @@ __device__ __forceinline__ void fb_body(const LkGeom &g, const uint8_t *__restri
 	}
 	if (score_map) return;
 	__syncthreads();
-	const int n = min(s_n, list_cap);
-	if (tid == 0 && n > 0) s_base = atomicAdd(&s.kp_count[stream * LK_BINS + bin], n);
-	__syncthreads();
-	if (n > 0) {
-		const int base = s_base;
-		uint32_t *list = s.kp + (stream * LK_BINS + bin) * (size_t)g.kp_cap;
-		for (int i = tid; i < n; i += THREADS)
-			if (base + i < g.kp_cap) list[base + i] = sL[i];
+	// Warp 0 alone appends the band's survivors (a few dozen) to the bin's list: the round trip of the reserving atomic is
+	// not a block-wide wait.  In the persistent kernels the other warps go on to the next item meanwhile: its first two
+	// barriers include warp 0, so the survivor buffer and s_n (reset by thread 0 at the top) are not touched before the
+	// copy below is done.
+	if (tid < 32) {
+		const int n = min(s_n, list_cap);
+		if (n > 0) {
+			int base = 0;
+			if (tid == 0) base = atomicAdd(&s.kp_count[stream * LK_BINS + bin], n);
+			base = __shfl_sync(0xFFFFFFFFu, base, 0);
+			uint32_t *list = s.kp + (stream * LK_BINS + bin) * (size_t)g.kp_cap;
+			for (int i = tid; i < n; i += 32)
+				if (base + i < g.kp_cap) list[base + i] = sL[i];
+		}
 	}
 }
 
@@ -294,8 +300,7 @@ lk_fast_band_masked_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, 
 		const uint32_t sb = item / (uint32_t)bands;
 		fb_body<THREADS, PC>(g, l0, s, nullptr, bands, P_rt, list_cap, (size_t)(sb >> 4), (int)(sb & 15u), (int)(item - sb * bands),
 				     s.plan_units + (size_t)item * g.fb_ucap, hdr);
-		__syncthreads();                                    // the next item reuses the shared-memory tiles and counters
-		item = item_n; hdr = hdr_n;
+		item = item_n; hdr = hdr_n;                         // (no barrier: see the end of fb_body)
 	}
 }
 
