@@ -521,6 +521,39 @@ def time_e2e(call, first, steps, world, rank, min_s=MIN_TIMED_S):
     return max_over_ranks((time.perf_counter() - t0) * 1e3, world), steps, res
 
 
+def host_threaded_run(make, frames, n, n_devices, min_s=MIN_TIMED_S):
+    """n_devices x n streams end to end through aof_*_create_multi from THIS process: pinned host frames in, every device's
+    records in the library's one pinned array out.  -> dict"""
+    import torch
+    devices = [spread_device(r, torch.cuda.device_count()) for r in range(n_devices)]
+    rot = min(2, frames.shape[0])
+    per = frames[0].size // n                                            # bytes per frame
+    keep = torch.empty((rot, n_devices * n, per), dtype=torch.uint8, pin_memory=True)
+    host = keep.numpy()
+    for k in range(rot):
+        for d in range(n_devices):
+            host[k, d * n:(d + 1) * n] = frames[k].reshape(n, per)
+    m = make(n_devices * n, devices)
+    t_us = np.zeros(n_devices * n, np.uint32)
+    for k in range(3):
+        m.calc_flow_batch(host[k % rot], t_us + 1000 * k, copy=False)
+    t0 = time.perf_counter(); m.calc_flow_batch(host[1 % rot], t_us + 3000, copy=False); probe = time.perf_counter() - t0
+    steps = int(max(3, min(2000, np.ceil(min_s / max(probe, 1e-6)))))
+    t0 = time.perf_counter()
+    for k in range(steps):
+        res = m.calc_flow_batch(host[k % rot], t_us + 1000 * (k + 4), copy=False)
+    dt = time.perf_counter() - t0
+    assert res.size == n_devices * n and (res["quality"] > 60).mean() > 0.97
+    out = {"value": n_devices * n * steps / dt, "unit": "frame-pairs/s", "steps": steps, "ms_per_step": dt / steps * 1e3,
+           "devices": devices, "ranges": m.ranges(), "h2d_bytes_per_step": n_devices * n * per + 4 * n_devices * n,
+           "d2h_bytes_per_step": 16 * n_devices * n,
+           "api": "aof_*_create_multi + aof_*_multi_calc_flow_batch: one process, a host worker thread per device, results in the "
+                  "library's one pinned array (host gather inside the call)"}
+    m.close()
+    del keep
+    return out
+
+
 def host_threaded_leg(make, frames, n, world, rank, min_s=MIN_TIMED_S):
     """The same end-to-end workload through the library's own multi-GPU entry points (aof_*_create_multi: ONE process, one
     host worker thread per device, every device's D2H landing in one pinned result array = the host gather, no torch and no
@@ -531,34 +564,43 @@ def host_threaded_leg(make, frames, n, world, rank, min_s=MIN_TIMED_S):
     import torch.distributed as dist
     torch.cuda.synchronize()
     dist.barrier(group=HOST_GROUP)          # host-side: the waiting ranks must not spin in a kernel on the GPUs rank 0 is about to use
-    out = None
-    if rank == 0:
-        devices = [spread_device(r, torch.cuda.device_count()) for r in range(world)]
-        rot = min(2, frames.shape[0])
-        per = frames[0].size // n                                        # bytes per frame
-        keep = torch.empty((rot, world * n, per), dtype=torch.uint8, pin_memory=True)
-        host = keep.numpy()
-        for k in range(rot):
-            for d in range(world):
-                host[k, d * n:(d + 1) * n] = frames[k].reshape(n, per)
-        m = make(world * n, devices)
-        t_us = np.zeros(world * n, np.uint32)
-        for k in range(3):
-            m.calc_flow_batch(host[k % rot], t_us + 1000 * k, copy=False)
-        t0 = time.perf_counter(); m.calc_flow_batch(host[1 % rot], t_us + 3000, copy=False); probe = time.perf_counter() - t0
-        steps = int(max(3, min(2000, np.ceil(min_s / max(probe, 1e-6)))))
-        t0 = time.perf_counter()
-        for k in range(steps):
-            res = m.calc_flow_batch(host[k % rot], t_us + 1000 * (k + 4), copy=False)
-        dt = time.perf_counter() - t0
-        assert res.size == world * n and (res["quality"] > 60).mean() > 0.97
-        out = {"value": world * n * steps / dt, "unit": "frame-pairs/s", "steps": steps, "devices": devices, "ranges": m.ranges(),
-               "api": "aof_*_create_multi + aof_*_multi_calc_flow_batch: one process, a host worker thread per device, results in the "
-                      "library's one pinned array (host gather inside the call)"}
-        m.close()
-        del keep
+    out = host_threaded_run(make, frames, n, world, min_s) if rank == 0 else None
     dist.barrier(group=HOST_GROUP)
     return out
+
+
+def run_single_process(args):
+    """python bench.py --gpus N without torchrun: ONE process drives N GPUs through aof_*_create_multi (host worker threads
+    inside the library, no torch.distributed, no NCCL).  Only the end-to-end metric exists in this mode (the entry points
+    take host frames); the device-resident value and the rooflines come from the per-GPU arm (torchrun or --gpus 1)."""
+    pkg = entry.load_package()
+    res = {}
+    if args.workload in ("lk", "both"):
+        n = args.lk_streams
+        keep, h_frames = pinned_frames((2, n, LK_H, LK_W))
+        lk_host_frames(n, 2, seed=2000, out=h_frames)
+        res["lk"] = host_threaded_run(lambda total, devs: pkg.LkFlowMulti(FX, FY, -1, LK_W, LK_H, LK_FEATURES, n_streams=total, devices=devs),
+                                      h_frames, n, args.gpus)
+        res["lk"]["workload"] = workload_name("lk", n)
+    if args.workload in ("sad", "both"):
+        n = SAD_STREAMS
+        frames, _ = sad_host_frames(n, 2, seed=1000)
+        res["sad"] = host_threaded_run(lambda total, devs: pkg.Px4FlowMulti(FX, FY, -1, SAD_W, SAD_H, SAD_SEARCH, 30, 3000, n_streams=total, devices=devs),
+                                       frames, n, args.gpus)
+        res["sad"]["workload"] = workload_name("sad", n)
+    p = res["sad" if args.workload == "sad" else "lk"]
+    line = {"metric": "frame-pairs/s", "value": p["value"], "unit": "frame-pairs/s", "n_gpus": args.gpus, "steps": p["steps"],
+            "warmup": 4, "ms_per_step": p["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": p["workload"], "mode": "single process, host-threaded multi-GPU entry points (aof_*_create_multi); "
+                       "value == e2e: host frames in, gathered records out", "devices": p["devices"]},
+            "roofline": None,
+            "e2e": {"value": p["value"], "unit": "frame-pairs/s", "h2d_bytes_per_step": p["h2d_bytes_per_step"],
+                    "d2h_bytes_per_step": p["d2h_bytes_per_step"], "api": p["api"]},
+            "gpu_launches": int(pkg.lib().aof_launch_count())}
+    if args.workload == "both":
+        line["sad"] = res["sad"]
+    print(json.dumps(line))
 
 
 def find_kernel(kb, prefix):
@@ -905,6 +947,9 @@ def main():
         if args.workload == "both":
             args.workload = "lk"
         run_reference(args)
+        return
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        run_single_process(args)
         return
     rank, world, local = dist_setup()
     with_cpu = world == 1 and not args.no_cpu
