@@ -130,6 +130,21 @@ int aof_px4_compute_flow_pairs_device(aof_px4 *h, const uint8_t *d_prev, const u
 /* forget previous frames and limiter state (as a freshly constructed object) */
 int aof_px4_reset(aof_px4 *h);
 
+/* The flow of n independent (previous, current) pairs WITHOUT ANY ALLOCATION: no handle, no cudaMalloc / cudaFree, no
+ * allocating library routine -- for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  No counterpart in the reference.
+ * out[i] is what a freshly constructed OpticalFlowPX4(p) returns from its SECOND calcFlow call when fed prev[i] and
+ * then cur[i] at time t_us[i] (= aof_px4_calc_flow_device on a new handle, called with prev, then with cur): quality,
+ * dt_us, flow_x, flow_y under p->output_rate.  The scratch between the two kernels (16 B of raw flow + 24 B of limiter
+ * state per pair) lives in one fixed __device__ array of AOF_STATIC_MAX_PAIRS pairs (320 KiB, held by every GPU that
+ * loads the library until exit): n beyond that is AOF_ERR_INVALID.  All calls on a GPU share the array, so calls that
+ * overlap on the GPU (two streams / two threads on one device) race -- serialise them.  d_prev / d_cur: n frames each,
+ * DEVICE pointers, 16-byte aligned; d_t_us, d_out: n entries, DEVICE pointers; asynchronous on cuda_stream. */
+#define AOF_STATIC_MAX_PAIRS 8192
+int aof_px4_static_max_pairs(void);
+int aof_px4_calc_flow_pairs_static(const aof_px4_params *p, int device, const uint8_t *d_prev, const uint8_t *d_cur,
+				   const uint32_t *d_t_us, int n, aof_flow_out *d_out, void *cuda_stream);
+
 /* replaces OpticalFlow::setFocalLengthX / setFocalLengthY / setOutputRate (include/optical_flow.hpp:76-78) on a
  * live handle: plain assignments, as in the reference -- previous frames, limiter sums and the time of the last
  * publish are kept; the new values apply from the next calc call, to all streams. */
