@@ -3,6 +3,7 @@
 #include <climits>
 #include <cstdint>
 #include <cuda_runtime.h>
+#include <utility>
 
 #include "../../include/aof.h"
 
@@ -76,6 +77,20 @@ enum KernelId {
 // brackets one launch with two events when timing is enabled; a no-op otherwise
 bool timing_on(); // per-kernel event timing requested (aof_timing_enable)
 
+// kernel<<<grid, block, smem, st>>>(args...), optionally with programmatic stream serialisation (the kernel must call
+// pdl_enter() before it touches global memory)
+template <typename... Exp, typename... Act>
+inline cudaError_t launch_k(bool pdl, void (*kernel)(Exp...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Act &&... args)
+{
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+	cudaLaunchAttribute at[1];
+	at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	at[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+	return cudaLaunchKernelEx(&cfg, kernel, std::forward<Act>(args)...);
+}
+
 class KernelTimer {
 public:
 	// `symbol`: the __global__ function this launch runs (what a profiler lists); aof_timing_read reports it for the slot
@@ -130,6 +145,7 @@ struct LkGeom {
 	int tun_pyr_v1;    // AOF_PYR_V1 = 1: the generic streaming kernel
 	int tun_fast_v1;   // AOF_FAST_V1 = 1: the tile FAST kernel
 	int tun_track_v1;  // AOF_TRACK_V1 = 1: the CTA-per-stream tracker
+	int tun_pdl;       // AOF_LK_PDL = 0: plain stream-ordered launches (default 1: programmatic dependent launch, pdl_enter())
 	int tun_fast_lazy; // AOF_FAST_LAZY = 0: score every pixel of the needed bins; 1: lazy arg-max (lk_fast_lazy.cu); 2 (default): masked band FAST
 };
 

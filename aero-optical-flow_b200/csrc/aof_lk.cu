@@ -168,7 +168,7 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	const size_t nN = (size_t)n_streams * N;
 	// every environment switch of this path is read here, once (never on a launch path)
 	g.tun_pyr_bands = env_int("AOF_PYR_BANDS", 0); g.tun_pyr_occ = env_int("AOF_PYR_OCC", 0);
-	g.tun_fast_lazy = env_int("AOF_FAST_LAZY", 2);
+	g.tun_fast_lazy = env_int("AOF_FAST_LAZY", 2); g.tun_pdl = env_int("AOF_LK_PDL", 1);
 	g.tun_pyr_v1 = env_int("AOF_PYR_V1", 0); g.tun_fast_v1 = env_int("AOF_FAST_V1", 0); g.tun_track_v1 = env_int("AOF_TRACK_V1", 0);
 	h->tun_split = env_int("AOF_LK_SPLIT", 0); h->tun_parts = env_int("AOF_LK_PARTS", 0);
 	cudaError_t e;

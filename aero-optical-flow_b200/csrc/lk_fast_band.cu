@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, uint8_t *__restrict__ score_map, int bands, int P_rt,
 		    int list_cap)
 {
+	pdl_enter();
 	const int bin = blockIdx.x / bands;
 	fb_body<THREADS, PC>(g, l0, s, score_map, bands, P_rt, list_cap, blockIdx.y, bin, blockIdx.x - bin * bands, nullptr, 0u);
 }
@@ -287,6 +288,7 @@ template <int THREADS, int PC>
 __global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_masked_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, int bands, int P_rt, int list_cap)
 {
+	pdl_enter();
 	const int n_work = s.n_work[0];
 	int w = blockIdx.x;
 	// the item and its header are two dependent global round trips: those of the NEXT item are issued before this item's
@@ -311,6 +313,7 @@ constexpr int FP_THREADS = 128;
 __global__ void __launch_bounds__(FP_THREADS)
 lk_fast_plan_kernel(LkGeom g, LkState s)
 {
+	pdl_enter();
 	extern __shared__ __align__(16) uint32_t fp_mask[];           // bh x mw words (mw = mask words per row + 1)
 	__shared__ short2 s_ex[LK_MAX_FEATURES];
 	__shared__ int s_nex;
@@ -427,6 +430,7 @@ template <int THREADS, int PC>
 __global__ void __launch_bounds__(THREADS, 1280 / THREADS)
 lk_fast_band_flagged_kernel(LkGeom g, const uint8_t *__restrict__ l0, LkState s, int bands, int P_rt, int list_cap)
 {
+	pdl_enter();
 	const int n_flag = s.n_full[0];
 	const int per_stream = LK_BINS * bands;
 	for (int w = blockIdx.x; w < n_flag * per_stream; w += gridDim.x) {
@@ -468,7 +472,7 @@ static cudaError_t fb_launch(const LkGeom &g, const uint8_t *l0, const LkState &
 	}
 	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
 	dim3 grid(LK_BINS * bands, n);
-	lk_fast_band_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, score_map, bands, P, cap);
+	launch_k(g.tun_pdl != 0, lk_fast_band_kernel<THREADS, PC>, grid, THREADS, smem, st, g, l0, s, score_map, bands, P, cap);
 	return cudaGetLastError();
 }
 
@@ -491,7 +495,7 @@ static cudaError_t fb_launch_flagged(const LkGeom &g, const uint8_t *l0, const L
 	const int bands = (g.bh - 6 + FB_ROWS - 1) / FB_ROWS;
 	long long items = (long long)n * LK_BINS * bands;
 	const int grid = (int)(items < grid_dev[dev] ? items : grid_dev[dev]);
-	lk_fast_band_flagged_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, bands, P, cap);
+	launch_k(g.tun_pdl != 0, lk_fast_band_flagged_kernel<THREADS, PC>, grid, THREADS, smem, st, g, l0, s, bands, P, cap);
 	return cudaGetLastError();
 }
 
@@ -514,7 +518,7 @@ static cudaError_t fb_launch_masked(const LkGeom &g, const uint8_t *l0, const Lk
 	}
 	const long long items = (long long)n * LK_BINS * g.fb_bands;
 	const int grid = (int)(items < grid_dev[dev] ? items : grid_dev[dev]);
-	lk_fast_band_masked_kernel<THREADS, PC><<<grid, THREADS, smem, st>>>(g, l0, s, g.fb_bands, P, cap);
+	launch_k(g.tun_pdl != 0, lk_fast_band_masked_kernel<THREADS, PC>, grid, THREADS, smem, st, g, l0, s, g.fb_bands, P, cap);
 	return cudaGetLastError();
 }
 
@@ -535,7 +539,7 @@ cudaError_t lk_fast_masked_launch(const LkGeom &g, const uint8_t *l0, const LkSt
 	if (n <= 0) return cudaSuccess;
 	{
 		KernelTimer kt(KID_LK_FAST_PLAN, st, "lk_fast_plan_kernel");
-		lk_fast_plan_kernel<<<dim3(LK_BINS, n), FP_THREADS, fp_smem_bytes(g), st>>>(g, s);
+		launch_k(g.tun_pdl != 0, lk_fast_plan_kernel, dim3(LK_BINS, n), FP_THREADS, fp_smem_bytes(g), st, g, s);
 		count_launch();
 		cudaError_t e = cudaGetLastError();
 		if (e != cudaSuccess) return e;

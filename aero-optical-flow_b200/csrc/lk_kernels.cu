@@ -469,6 +469,7 @@ constexpr int TS_WARPS = AOF_TS_WARPS;
 __global__ void __launch_bounds__(TS_WARPS * 32, AOF_TS_MINB)
 lk_track_split_kernel(LkGeom g, LkPyr prev, LkPyr next, LkState s, int have_prev, int groups)
 {
+	pdl_enter();
 	__shared__ LkWarpScratch s_sc[TS_WARPS];
 	__shared__ int s_per_bin[LK_BINS];
 	__shared__ int s_last, s_target;
@@ -550,7 +551,7 @@ cudaError_t lk_track_update_launch(const LkGeom &g, const LkPyr &prev, const LkP
 	if (g.tun_track_v1 == 1) lk_track_update_kernel<<<n, TU_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev);
 	else {
 		const int groups = (g.n_feat + TS_WARPS - 1) / TS_WARPS;
-		lk_track_split_kernel<<<n * groups, TS_WARPS * 32, 0, st>>>(g, prev, next, s, have_prev, groups);
+		launch_k(g.tun_pdl != 0, lk_track_split_kernel, n * groups, TS_WARPS * 32, 0, st, g, prev, next, s, have_prev, groups);
 	}
 	count_launch();
 	return cudaGetLastError();
@@ -776,6 +777,7 @@ lk_select_epilogue_kernel(LkGeom g, LkState s, const uint32_t *__restrict__ t_us
 			  aof_lk_raw *__restrict__ raw, int have_feat_prev, int output_rate, float conf, float focal_x,
 			  float focal_y, LkCamera cam, int mode)
 {
+	pdl_enter();
 	__shared__ int s_ex[LK_MAX_FEATURES], s_ey[LK_MAX_FEATURES];
 	__shared__ int s_nex, s_ngood, s_done;
 	__shared__ int s_needed[LK_BINS], s_cnt[LK_BINS], s_npick[LK_BINS];
@@ -1084,7 +1086,7 @@ cudaError_t lk_select_epilogue_launch(const LkGeom &g, const LkState &s, const u
 {
 	if (n <= 0) return cudaSuccess;
 	KernelTimer kt(KID_LK_SELECT_EPILOGUE, st);
-	lk_select_epilogue_kernel<<<n, SEL_THREADS, 0, st>>>(g, s, t_us, out, raw, have_feat_prev, output_rate, conf, fx, fy, cam, mode);
+	launch_k(g.tun_pdl != 0, lk_select_epilogue_kernel, n, SEL_THREADS, 0, st, g, s, t_us, out, raw, have_feat_prev, output_rate, conf, fx, fy, cam, mode);
 	count_launch();
 	return cudaGetLastError();
 }

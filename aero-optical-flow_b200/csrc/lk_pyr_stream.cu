@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(PS_WARPS * 32)
 lk_pyr_stream_kernel(LkGeom g, const uint8_t *__restrict__ l0, uint8_t *__restrict__ l1, uint8_t *__restrict__ l2,
 		     uint8_t *__restrict__ l3, PsStrips ss, int bands, int band_rows, int n_tasks)
 {
+	pdl_enter();
 	const int lane = threadIdx.x & 31;
 	const int task = blockIdx.x * PS_WARPS + (threadIdx.x >> 5);
 	if (task >= n_tasks) return;
@@ -291,6 +292,7 @@ __global__ void __launch_bounds__(PS_WARPS * 32, MIN_CTAS)
 lk_pyr_stream16_kernel(LkGeom g, const uint8_t *__restrict__ l0, uint8_t *__restrict__ l1, uint8_t *__restrict__ l2,
 		       uint8_t *__restrict__ l3, PsStrips ss, int bands, int band_rows, int n_tasks)
 {
+	pdl_enter();
 	const int lane = threadIdx.x & 31;
 	const int task = blockIdx.x * PS_WARPS + (threadIdx.x >> 5);
 	if (task >= n_tasks) return;
@@ -461,11 +463,12 @@ cudaError_t lk_pyr_stream_launch(const LkGeom &g, const uint8_t *l0, uint8_t *l1
 	const int o = g.tun_pyr_occ > 0 ? g.tun_pyr_occ : 16; // measured on B200: 16 CTAs/SM (<= 128 registers) is the fastest
 	KernelTimer kt(KID_LK_PYR_FUSED, st, !rows16 ? "lk_pyr_stream_kernel" : o <= 16 ? "lk_pyr_stream16_kernel<16>" : o <= 20 ? "lk_pyr_stream16_kernel<20>" : "lk_pyr_stream16_kernel<24>");
 	if (rows16) {
-		if (o <= 16) lk_pyr_stream16_kernel<16><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
-		else if (o <= 20) lk_pyr_stream16_kernel<20><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
-		else lk_pyr_stream16_kernel<24><<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+		const bool pdl = g.tun_pdl != 0;
+		if (o <= 16) launch_k(pdl, lk_pyr_stream16_kernel<16>, blocks, PS_WARPS * 32, 0, st, g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+		else if (o <= 20) launch_k(pdl, lk_pyr_stream16_kernel<20>, blocks, PS_WARPS * 32, 0, st, g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+		else launch_k(pdl, lk_pyr_stream16_kernel<24>, blocks, PS_WARPS * 32, 0, st, g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 	} else
-		lk_pyr_stream_kernel<<<blocks, PS_WARPS * 32, 0, st>>>(g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
+		launch_k(g.tun_pdl != 0, lk_pyr_stream_kernel, blocks, PS_WARPS * 32, 0, st, g, l0, l1, l2, l3, ss, bands, band_rows, (int)tasks);
 	count_launch();
 	return cudaGetLastError();
 }
