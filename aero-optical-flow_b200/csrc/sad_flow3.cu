@@ -41,6 +41,14 @@ __host__ __device__ constexpr uint32_t row_off(int y) { return (uint32_t)(y * W 
 // window row r of any block: y = 1 + 10 by + r, so the gap count is by + (r >= 9): static in r up to a per-lane base
 __host__ __device__ constexpr uint32_t wrow(int r) { return (uint32_t)(r * W + (r >= 9 ? GAP : 0)); }
 
+// u / 5 and u / 10 for u < 64 as one multiply and one shift.  The per-lane set-up below runs ONCE per warp, and at 4096 pairs
+// per launch a warp owns one pair: with plain / and % the compiler spent ~600 of the 3 300 warp instructions per pair on it
+// (16-bit division sequences for seven rounds of block indices, profiles/r2R_*).
+__device__ __forceinline__ uint32_t div5(uint32_t u) { return (u * 205u) >> 10; }
+__device__ __forceinline__ uint32_t div10(uint32_t u) { return (u * 205u) >> 11; }
+// row_off(y) for a run-time y < 64
+__device__ __forceinline__ uint32_t row_off_rt(uint32_t y) { return (y + div10(y)) * (uint32_t)W; }
+
 __device__ __forceinline__ uint32_t havg4_3(uint32_t a, uint32_t b, uint32_t half)
 {
 	uint32_t r;
@@ -102,13 +110,13 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 	__shared__ uint16_t s_rowoff[H];                    // row_off(y), for the data-dependent rows of the half-pixel stage
 	__shared__ __align__(8) uint64_t s_bar;
 
-	const int lane = threadIdx.x;
+	const uint32_t lane = threadIdx.x;
 	const uint32_t sc = smem_u32(s_frame);
 	const uint32_t sa = smem_u32(&s_ablk[0][0]);
 
 	if (lane == 0) mbar_init(&s_bar, 1);
-	s_rowoff[lane] = (uint16_t)row_off(lane);
-	s_rowoff[lane + 32] = (uint16_t)row_off(lane + 32);
+	s_rowoff[lane] = (uint16_t)row_off_rt(lane);
+	s_rowoff[lane + 32] = (uint16_t)row_off_rt(lane + 32);
 	__syncwarp();
 
 	// ---- per-lane task constants (the same for every pair) ----
@@ -116,21 +124,22 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 	uint32_t pw[3], psh[3], pm[3], pa[3];
 #pragma unroll
 	for (int k = 0; k < 3; k++) {
-		const int t = lane + 32 * k, b = t >> 2, p = t & 3;
-		const int bx = b % NB, by = b / NB;
-		const uint32_t o = (uint32_t)(1 + STEP * bx + 2 * p);
-		pw[k] = sc + row_off(1 + STEP * by) + (o & ~3u);
+		const uint32_t b = (lane >> 2) + 8u * k, p = lane & 3u;      // task t = lane + 32 k
+		const uint32_t by = div5(b), bx = b - NB * by;
+		const uint32_t o = 1u + STEP * bx + 2u * p;
+		pw[k] = sc + (uint32_t)W + by * (uint32_t)(STEP * W + GAP) + (o & ~3u);   // row_off(1 + 10 by) = 64 + 704 by
 		psh[k] = (o & 3u) * 8;
 		pm[k] = 1u << (24 - 8 * (o & 3u));
 		pa[k] = sa + b * (APITCH * 4);
 	}
 	// single round: lanes 0..24 = (block lane, dx index 8), lanes 25..31 = (block 24, dx index lane - 25)
-	const int sb = lane < NBLK ? lane : NBLK - 1, sdx = lane < NBLK ? 8 : lane - NBLK;
-	const uint32_t so = (uint32_t)(1 + STEP * (sb % NB) + sdx);
-	const uint32_t sw = sc + row_off(1 + STEP * (sb / NB)) + (so & ~3u), ssh = (so & 3u) * 8, saddr = sa + sb * (APITCH * 4);
+	const uint32_t sb = lane < NBLK ? lane : NBLK - 1, sdx = lane < NBLK ? 8u : lane - NBLK;
+	const uint32_t sby = div5(sb), sbx = sb - NB * sby;
+	const uint32_t so = 1u + STEP * sbx + sdx;
+	const uint32_t sw = sc + (uint32_t)W + sby * (uint32_t)(STEP * W + GAP) + (so & ~3u), ssh = (so & 3u) * 8, saddr = sa + sb * (APITCH * 4);
 	// leftover: (block 24, dx index 7) split by dy over lanes 0..8
 	const uint32_t lo_o = (uint32_t)(1 + STEP * 4 + 7);
-	const uint32_t lw = sc + row_off(1 + STEP * 4 + min(lane, 8)) + (lo_o & ~3u), lsh = (lo_o & 3u) * 8;
+	const uint32_t lw = sc + row_off_rt(1u + STEP * 4 + min(lane, 8u)) + (lo_o & ~3u), lsh = (lo_o & 3u) * 8;
 
 	uint32_t parity = 0;
 	for (int pair = blockIdx.x; pair < n; pair += gridDim.x, parity ^= 1u) {
@@ -150,16 +159,18 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 			uint32_t w0[A1_ROUNDS], w1[A1_ROUNDS], w2[A1_ROUNDS];
 #pragma unroll
 			for (int k = 0; k < A1_ROUNDS; k++) {
-				const int task = min(k * 32 + lane, NBLK * 8 - 1), b = task >> 3;
-				const uint32_t off = (uint32_t)((LO + STEP * (b / NB) + (task & 7)) * W + LO + STEP * (b % NB));
+				const uint32_t task = min(k * 32u + lane, (uint32_t)(NBLK * 8 - 1)), b = task >> 3;
+				const uint32_t by = div5(b), bx = b - NB * by;
+				const uint32_t off = (LO + STEP * by + (task & 7u)) * W + LO + STEP * bx;
 				const uint32_t *w = reinterpret_cast<const uint32_t *>(pf + (off & ~3u));
 				w0[k] = __ldg(w); w1[k] = __ldg(w + 1); w2[k] = __ldg(w + 2);
 			}
 #pragma unroll
 			for (int k = 0; k < A1_ROUNDS; k++) {
-				const int task = k * 32 + lane, b = task >> 3;
+				const uint32_t task = k * 32u + lane, b = task >> 3;
 				if (task < NBLK * 8) {
-					const uint32_t sh = (uint32_t)(LO + STEP * (b % NB)) & 3u; // 5 + 10 bx: 1 or 3
+					const uint32_t bx = b - NB * div5(b);
+					const uint32_t sh = 1u + 2u * (bx & 1u);                   // (5 + 10 bx) & 3: 1 or 3
 					s_ablk[b][2 * (task & 7)] = bytes_at(w0[k], w1[k], sh);
 					s_ablk[b][2 * (task & 7) + 1] = bytes_at(w1[k], w2[k], sh);
 				}
@@ -292,7 +303,8 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 			const int task = base + lane;
 			const bool live = task < NBLK * 2;
 			const int b = live ? task >> 1 : 0, half = task & 1;
-			const int x = LO + STEP * (b % NB), y = LO + STEP * (b / NB);
+			const int by_ = (int)div5((uint32_t)b);
+			const int x = LO + STEP * (b - NB * by_), y = LO + STEP * by_;
 			const uint32_t tex = s_tex[b];
 			uint32_t best_sad = 0xFFFFFFFFu;
 			int dx = 0, dy = 0, subdir = 8, accepted = 0;
