@@ -122,6 +122,16 @@ cudaError_t px4_epilogue_launch(const aof_px4_raw *raw, const uint32_t *t_us, Li
 // LK path (OpticalFlowOpenCV::calcFlow, trackFeatures, calcOpticalFlowPyrLK, FAST)
 namespace aof {
 
+// band FAST kernel (lk_fast_band.cu): output rows per band, threads of the masked kernel on 640-px frames.  Measured (r2Y,
+// masked kernel per 512 LK streams): 38 rows x 320 threads (4 CTAs / SM) 274.6 us; 19 x 160 (8 / SM) 283.1; 26 x 256 (5 / SM)
+// 311.1; 19 x 320 336.9 -- more, smaller CTAs do not pay for their extra halo rows.
+#ifndef AOF_FB_ROWS
+#define AOF_FB_ROWS 38
+#endif
+#ifndef AOF_FB_MTHREADS
+#define AOF_FB_MTHREADS 320
+#endif
+constexpr int FB_ROWS = AOF_FB_ROWS;
 constexpr int LK_MAX_LEVELS = 4;   // maxLevel = 3 (trackFeatures.cpp:98)
 constexpr int LK_WIN = 9;          // Size(9, 9)
 constexpr int LK_MAX_FEATURES = 100; // trackFeatures.cpp:56

@@ -142,8 +142,8 @@ int aof_lk_create(const aof_lk_params *p, int n_streams, int device, aof_lk **ou
 	LkGeom &g = h->g;
 	g.n_feat = N; g.bw = W / 4; g.bh = H / 4; g.tpb = tpb; g.dist = g.bw / tpb; g.fast_thr = 10;
 	g.kp_cap = ((g.bw + 1) / 2) * ((g.bh + 1) / 2);
-	g.fb_bands = g.bh > 6 ? (g.bh - 6 + 37) / 38 : 1;
-	g.fb_ucap = 40 * ((g.bw / 2 + 15) / 16);
+	g.fb_bands = g.bh > 6 ? (g.bh - 6 + FB_ROWS - 1) / FB_ROWS : 1;
+	g.fb_ucap = (FB_ROWS + 2) * ((g.bw / 2 + 15) / 16);
 	if (g.bw > 4096 || g.bh > 4096) { // keypoint entries carry 12-bit bin-local coordinates
 		delete h;
 		set_error("frame %dx%d too large: bins above 4096 px", W, H);

@@ -40,7 +40,7 @@
 
 namespace aof {
 
-constexpr int FB_ROWS = 38;             // output rows per band (a 120-row bin has 114 = 3 x 38)
+// FB_ROWS (aof_internal.h): output rows per band (38: a 120-row bin has 114 = 3 x 38)
 constexpr int FB_SROWS = FB_ROWS + 2;   // response rows (one above, one below for the suppression)
 constexpr int FB_PROWS = FB_ROWS + 8;   // pixel rows
 constexpr int FB_MAX_GROUPS = 20;       // row groups: thread = (group, pair column); THREADS / (bw / 2) of them
@@ -547,7 +547,7 @@ cudaError_t lk_fast_masked_launch(const LkGeom &g, const uint8_t *l0, const LkSt
 	const int npc = g.bw / 2;
 	KernelTimer kt(KID_LK_FAST, st, npc == 80 ? "lk_fast_band_masked_kernel<320,84>" : "lk_fast_band_masked_kernel");
 	count_launch();
-	if (npc == 80) return fb_launch_masked<320, 84>(g, l0, s, n, st);
+	if (npc == 80) return fb_launch_masked<AOF_FB_MTHREADS, 84>(g, l0, s, n, st);
 	if (4 * npc <= 320) return fb_launch_masked<320, 0>(g, l0, s, n, st);
 	if (4 * npc <= 640) return fb_launch_masked<640, 0>(g, l0, s, n, st);
 	return fb_launch_masked<1024, 0>(g, l0, s, n, st);
