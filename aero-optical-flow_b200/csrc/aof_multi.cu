@@ -31,6 +31,15 @@ using namespace aof;
 
 namespace {
 
+// The multi entry points touch every device from the CALLER's thread (create, destroy, state read-back): the caller's
+// current device is put back when they return, so that a caller (torch, for one) that tracks the current device itself
+// does not find it changed behind its back.
+struct DeviceGuard {
+	int dev = -1;
+	DeviceGuard() { if (cudaGetDevice(&dev) != cudaSuccess) { dev = -1; cudaGetLastError(); } }
+	~DeviceGuard() { if (dev >= 0) cudaSetDevice(dev); }
+};
+
 // one job = one batch call on one device
 struct Job {
 	const uint8_t *imgs = nullptr;
@@ -118,6 +127,7 @@ struct aof_multi {
 static void multi_destroy(aof_multi *m)
 {
 	if (!m) return;
+	DeviceGuard guard;
 	for (Worker *w : m->workers) {
 		if (w->th.joinable()) {
 			{ std::lock_guard<std::mutex> lk(w->mu); w->state = 3; }
@@ -142,6 +152,7 @@ static int multi_create(const aof_px4_params *pp, const aof_lk_params *lp, int n
 		return AOF_ERR_INVALID;
 	}
 	*out = nullptr;
+	DeviceGuard guard;
 	for (int i = 0; i < n_devices; i++)
 		for (int j = 0; j < i; j++)
 			if (devices[i] == devices[j]) { set_error("create_multi: device %d listed twice", devices[i]); return AOF_ERR_INVALID; }
@@ -260,6 +271,7 @@ int aof_lk_multi_set_params(aof_lk_multi *m, float fx, float fy, int rate, float
 int aof_lk_multi_get_state(aof_lk_multi *m, int32_t *update_vec, float *feat_cur, float *prev_corners, uint8_t *prev_status)
 {
 	if (!m) return AOF_ERR_INVALID;
+	DeviceGuard guard;
 	aof_multi *mm = reinterpret_cast<aof_multi *>(m);
 	for (Worker *w : mm->workers) {
 		const int N = aof_lk_num_features(w->lk);

@@ -97,20 +97,35 @@ __device__ __forceinline__ uint32_t key9(const uint32_t (&acc)[NI])
 #ifndef AOF_SAD3_MINB
 #define AOF_SAD3_MINB 28 // resident warps per SM the register allocation is capped for
 #endif
-__global__ void __launch_bounds__(32, AOF_SAD3_MINB)
+// warps per CTA: every warp is still autonomous (own frame slot, own mbarrier, no block barrier anywhere); the CTA only
+// groups them for the block scheduler.  Measured (r2a): 1, 2 or 4 warps per CTA give the same 27.0 / 160.2 us at 4096 / 32768 pairs.
+#ifndef AOF_SAD3_WPC
+#define AOF_SAD3_WPC 1
+#endif
+struct Sad3Slot {
+	alignas(128) uint8_t frame[SLOT_BYTES];
+	alignas(16) uint32_t ablk[NBLK][APITCH];            // aligned 8x8 blocks of prev
+	uint32_t key[NBLK];                                 // min over candidates of sad << 9 | candidate
+	uint32_t tex[NBLK];
+	int vote[NBLK][2];                                  // 2*dx + half, 2*dy + half (or INT_MIN)
+	uint16_t rowoff[H];                                 // row_off(y), for the data-dependent rows of the half-pixel stage
+	alignas(8) uint64_t bar;
+};
+__global__ void __launch_bounds__(32 * AOF_SAD3_WPC, AOF_SAD3_MINB / AOF_SAD3_WPC)
 sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ cur, size_t frame_stride, int n,
 		 uint32_t feat_thr, uint32_t val_thr, aof_px4_raw *__restrict__ raw, aof_px4_block *__restrict__ blocks,
 		 uint32_t half_mul /* 0x80000000, see havg4_3 */)
 {
-	__shared__ __align__(128) uint8_t s_frame[SLOT_BYTES];
-	__shared__ __align__(16) uint32_t s_ablk[NBLK][APITCH]; // aligned 8x8 blocks of prev
-	__shared__ uint32_t s_key[NBLK];                    // min over candidates of sad << 9 | candidate
-	__shared__ uint32_t s_tex[NBLK];
-	__shared__ int s_vote[NBLK][2];                     // 2*dx + half, 2*dy + half (or INT_MIN)
-	__shared__ uint16_t s_rowoff[H];                    // row_off(y), for the data-dependent rows of the half-pixel stage
-	__shared__ __align__(8) uint64_t s_bar;
+	__shared__ Sad3Slot s_slots[AOF_SAD3_WPC];
+	Sad3Slot &SL = s_slots[threadIdx.x >> 5];
+	uint8_t *const s_frame = SL.frame;
+	uint32_t (*const s_ablk)[APITCH] = SL.ablk;
+	uint32_t *const s_key = SL.key, *const s_tex = SL.tex;
+	int (*const s_vote)[2] = SL.vote;
+	uint16_t *const s_rowoff = SL.rowoff;
+	uint64_t &s_bar = SL.bar;
 
-	const uint32_t lane = threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t sc = smem_u32(s_frame);
 	const uint32_t sa = smem_u32(&s_ablk[0][0]);
 
@@ -142,7 +157,7 @@ sad_flow3_kernel(const uint8_t *__restrict__ prev, const uint8_t *__restrict__ c
 	const uint32_t lw = sc + row_off_rt(1u + STEP * 4 + min(lane, 8u)) + (lo_o & ~3u), lsh = (lo_o & 3u) * 8;
 
 	uint32_t parity = 0;
-	for (int pair = blockIdx.x; pair < n; pair += gridDim.x, parity ^= 1u) {
+	for (int pair = blockIdx.x * AOF_SAD3_WPC + (threadIdx.x >> 5); pair < n; pair += gridDim.x * AOF_SAD3_WPC, parity ^= 1u) {
 		// every lane finished reading the previous pair's frame before the __syncwarp that ended its phase C
 		if (lane == 0) mbar_expect_tx(&s_bar, H * W);
 		__syncwarp();
@@ -429,14 +444,15 @@ cudaError_t sad_flow3_launch(const uint8_t *prev, const uint8_t *cur, const SadG
 		int sms = 0, occ = 0;
 		if ((e = cudaFuncSetAttribute(sad_flow3_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess) return e;
 		if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-		if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sad_flow3_kernel, 32, 0)) != cudaSuccess) return e;
+		if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sad_flow3_kernel, 32 * AOF_SAD3_WPC, 0)) != cudaSuccess) return e;
 		grid_max[dev] = sms * (occ < 1 ? 1 : occ);
 		sms_dev[dev] = sms;
 	}
 	int gmax = grid_max[dev];
 	if (g.tun_ctas > 0 && g.tun_ctas * sms_dev[dev] < gmax) gmax = g.tun_ctas * sms_dev[dev];
-	const int grid = n < gmax ? n : gmax;
-	sad_flow3_kernel<<<grid, 32, 0, st>>>(prev, cur, g.frame_stride, n, g.feat_thr, g.val_thr, raw, blocks, 0x80000000u);
+	const int ctas = (n + AOF_SAD3_WPC - 1) / AOF_SAD3_WPC;
+	const int grid = ctas < gmax ? ctas : gmax;
+	sad_flow3_kernel<<<grid, 32 * AOF_SAD3_WPC, 0, st>>>(prev, cur, g.frame_stride, n, g.feat_thr, g.val_thr, raw, blocks, 0x80000000u);
 	return cudaGetLastError();
 }
 

@@ -21,12 +21,13 @@ def _bind(L):
 def _handle_path(pkg, prev, cur, t_us, rate, s):
     """the existing entry point: a fresh handle fed prev, then cur"""
     import torch
+    torch.cuda.set_device(0)                                  # (earlier tests may have left another device current)
     n = prev.shape[0]
     f = pkg.Px4Flow(FX, FY, rate, 64, 64, s, 30, 3000, n_streams=n)
-    d_prev, d_cur = torch.from_numpy(prev).cuda(), torch.from_numpy(cur).cuda()
-    d_t0 = torch.zeros(n, dtype=torch.int32, device="cuda")
-    d_t1 = torch.from_numpy(t_us.astype(np.int32)).cuda()
-    d_out = torch.zeros((n, 4), dtype=torch.int32, device="cuda")
+    d_prev, d_cur = torch.from_numpy(prev).to("cuda:0"), torch.from_numpy(cur).to("cuda:0")
+    d_t0 = torch.zeros(n, dtype=torch.int32, device="cuda:0")
+    d_t1 = torch.from_numpy(t_us.astype(np.int32)).to("cuda:0")
+    d_out = torch.zeros((n, 4), dtype=torch.int32, device="cuda:0")
     f.calc_flow_device(d_prev.data_ptr(), d_t0.data_ptr(), d_out.data_ptr())
     f.calc_flow_device(d_cur.data_ptr(), d_t1.data_ptr(), d_out.data_ptr())
     torch.cuda.synchronize()
@@ -39,11 +40,12 @@ def _static_path(pkg, prev, cur, t_us, rate, s):
     import torch
     L = pkg.capi.lib()
     _bind(L)
+    torch.cuda.set_device(0)
     n = prev.shape[0]
     p = pkg.capi.Px4Params(FX, FY, rate, 64, 64, s, 30, 3000)
-    d_prev, d_cur = torch.from_numpy(prev).cuda(), torch.from_numpy(cur).cuda()
-    d_t = torch.from_numpy(t_us.astype(np.int32)).cuda()
-    d_out = torch.full((n, 4), -7, dtype=torch.int32, device="cuda")
+    d_prev, d_cur = torch.from_numpy(prev).to("cuda:0"), torch.from_numpy(cur).to("cuda:0")
+    d_t = torch.from_numpy(t_us.astype(np.int32)).to("cuda:0")
+    d_out = torch.full((n, 4), -7, dtype=torch.int32, device="cuda:0")
     torch.cuda.synchronize()                                  # everything is allocated BEFORE the call under test
     rc = L.aof_px4_calc_flow_pairs_static(C.byref(p), 0, d_prev.data_ptr(), d_cur.data_ptr(), d_t.data_ptr(), n,
                                           d_out.data_ptr(), None)
@@ -72,12 +74,13 @@ def test_static_entry_point_rejects_what_it_cannot_hold(pkg):
     import torch
     L = pkg.capi.lib()
     _bind(L)
+    torch.cuda.set_device(0)
     cap = L.aof_px4_static_max_pairs()
     assert cap == 8192
     p = pkg.capi.Px4Params(FX, FY, -1, 64, 64, 4, 30, 3000)
-    buf = torch.zeros(64 * 64 * 4 + 16, dtype=torch.uint8, device="cuda")
-    t = torch.zeros(4, dtype=torch.int32, device="cuda")
-    out = torch.zeros((4, 4), dtype=torch.int32, device="cuda")
+    buf = torch.zeros(64 * 64 * 4 + 16, dtype=torch.uint8, device="cuda:0")
+    t = torch.zeros(4, dtype=torch.int32, device="cuda:0")
+    out = torch.zeros((4, 4), dtype=torch.int32, device="cuda:0")
     a = buf.data_ptr()
     assert L.aof_px4_calc_flow_pairs_static(C.byref(p), 0, a, a, t.data_ptr(), cap + 1, out.data_ptr(), None) != 0
     assert b"AOF_STATIC_MAX_PAIRS" in L.aof_last_error()
