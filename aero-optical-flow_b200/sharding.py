@@ -84,3 +84,64 @@ def max_over_ranks(value, world, dist=None, device="cpu"):
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+class ShmGather:
+    """The host gather of one box without a collective: ONE array in POSIX shared memory (a file under /dev/shm) that
+    every rank maps; a rank copies its records into its own slice and then publishes the step number in its own
+    sequence slot; rank 0 copies the array out once every slot has reached the step and acknowledges it.  Two buffers
+    alternate, so step k + 1 may be written while rank 0 still reads step k; put(k + 2) waits for the acknowledgement
+    of step k.  x86 stores are not reordered with other stores, and numpy's copies are plain stores: the sequence
+    number is written after the records.
+
+    Every rank constructs it with the same `path`; rank 0 creates the file BEFORE the others open it (the caller
+    places a barrier in between, bench.py does)."""
+
+    def __init__(self, path, total, world, rank, dtype, create=False):
+        self.total, self.world, self.rank, self.dtype = total, world, rank, np.dtype(dtype)
+        self.rec_bytes = 2 * total * self.dtype.itemsize
+        nbytes = 64 * world + self.rec_bytes                      # one cache line of sequence number per rank, then 2 buffers
+        if create:
+            with open(path, "wb") as f:
+                f.truncate(nbytes)
+        self.mm = np.memmap(path, dtype=np.uint8, mode="r+", shape=(nbytes,))
+        self.seq = self.mm[: 64 * world].view(np.int64).reshape(world, 8)
+        self.buf = self.mm[64 * world:].view(self.dtype).reshape(2, total)
+        self.lo, self.hi = shard_range(total, world, rank)
+        self.path = path
+
+    def put(self, local, step, timeout_s=60.0):
+        """this rank's records of `step` (1, 2, 3, ...).  Buffer step & 1 last held step - 2: the call waits until rank 0
+        has acknowledged reading it."""
+        assert len(local) == self.hi - self.lo
+        import time
+        t_end = time.monotonic() + timeout_s
+        while self.rank != 0 and int(self.seq[0, 1]) < step - 2:
+            if time.monotonic() > t_end:
+                raise TimeoutError("ShmGather.put: step %d, rank 0 has read up to %d" % (step, int(self.seq[0, 1])))
+        self.buf[step & 1, self.lo:self.hi] = local
+        self.seq[self.rank, 0] = step
+
+    def wait(self, step, timeout_s=60.0):
+        """rank 0: a copy of the records of all ranks for `step` (and the acknowledgement that frees the buffer);
+        other ranks: None"""
+        if self.rank != 0:
+            return None
+        import time
+        t_end = time.monotonic() + timeout_s
+        while int(self.seq[:, 0].min()) < step:
+            if time.monotonic() > t_end:
+                raise TimeoutError("ShmGather: step %d, sequence numbers %s" % (step, self.seq[:, 0].tolist()))
+        out = self.buf[step & 1].copy()
+        self.seq[0, 1] = step
+        return out
+
+    def close(self, unlink=False):
+        self.seq = self.buf = None
+        del self.mm
+        if unlink:
+            import os
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass

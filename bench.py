@@ -174,13 +174,25 @@ def dist_setup():
 HOST_GROUP = None
 
 
-def host_gather(res, rank, world):
-    """rank 0 receives every rank's result records (16 B per stream) over the host group: the 'host gather' of SURVEY.md
-    8(e) (aero-optical-flow_b200/sharding.py, covered on CPU by tests/test_sharding.py).  Non-blocking: -> a handle whose
-    wait() returns the records of all ranks in stream order on rank 0, None elsewhere."""
+_GATHER_SEQ = [0]
+
+
+def host_gather_open(sample, rank, world):
+    """The 'host gather' of SURVEY.md 8(e) for the ranks of one box: one array in POSIX shared memory that every rank
+    copies its 16-byte records into and rank 0 reads (aero-optical-flow_b200/sharding.py: ShmGather, covered on CPU by
+    tests/test_sharding.py) -- host memory only, no collective.  (The gloo form, sharding.gather_results, costs a
+    collective's latency per step, more than a whole 0.38 ms SAD step.)  -> gather object, None for one rank"""
+    if world == 1:
+        return None
     import torch.distributed as dist
-    return entry.load_package().sharding.gather_results_async(res, world * len(res), world, rank, dist if world > 1 else None,
-                                                              group=HOST_GROUP)
+    sh = entry.load_package().sharding
+    _GATHER_SEQ[0] += 1
+    path = "/dev/shm/aof_bench_gather_%s_%d.bin" % (os.environ.get("MASTER_PORT", "0"), _GATHER_SEQ[0])
+    g = sh.ShmGather(path, world * len(sample), world, rank, sample.dtype, create=True) if rank == 0 else None
+    dist.barrier(group=HOST_GROUP)                               # the file exists before the others map it
+    if rank != 0:
+        g = sh.ShmGather(path, world * len(sample), world, rank, sample.dtype)
+    return g
 
 
 def barrier(world):
@@ -500,25 +512,33 @@ def h2d_probe(keep, world):
 
 def time_e2e(call, first, steps, world, rank, min_s=MIN_TIMED_S):
     """host-API steps (synchronous calls: H2D, kernels, D2H inside) between barriers, wall clock, max over ranks; every
-    step's records are gathered on rank 0 over the host group, one gather in flight while the next step runs, the last
-    one awaited inside the timed region.  The step count is raised until min_s is timed.
-    -> (ms total, steps timed, last gathered result (rank 0) )"""
+    step's records are gathered on rank 0 through host shared memory (host_gather_open), rank 0 reading step k - 1 after
+    its own step k, the last step awaited inside the timed region.  The step count is raised until min_s is timed.
+    -> (ms total, steps timed, last gathered result on rank 0)"""
     import torch
+    import torch.distributed as dist
     barrier(world)
-    t0 = time.perf_counter(); res = host_gather(call(first), rank, world).wait(); probe = time.perf_counter() - t0
+    t0 = time.perf_counter(); res = call(first); probe = time.perf_counter() - t0
     probe = max_over_ranks(probe * 1e3, world) * 1e-3
     steps = int(max(steps, min(2000, np.ceil(min_s / max(probe, 1e-6)))))
+    g = host_gather_open(res, rank, world)
     barrier(world)
     t0 = time.perf_counter()
-    pending = None
     for k in range(steps):
-        h = host_gather(call(first + 1 + k), rank, world)
-        if pending is not None:
-            res = pending.wait()
-        pending = h
-    res = pending.wait()
+        res = call(first + 1 + k)
+        if g is not None:
+            g.put(res, k + 1)
+            if k >= 1:
+                g.wait(k)
+    if g is not None:
+        out = g.wait(steps)
+        res = out if rank == 0 else None
     torch.cuda.synchronize()
-    return max_over_ranks((time.perf_counter() - t0) * 1e3, world), steps, res
+    ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+    if g is not None:
+        dist.barrier(group=HOST_GROUP)
+        g.close(unlink=rank == 0)
+    return ms, steps, res
 
 
 def host_threaded_run(make, frames, n, n_devices, min_s=MIN_TIMED_S):
@@ -743,7 +763,7 @@ def run_sad_gpu(args, rank, world, local, with_cpu, n_streams=None, light=False)
         "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": 16 * n, "steps": e_steps,
                 "api": "aof_px4_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
-                       (", every step's records gathered on rank 0 over the host (gloo) group, one gather in flight under the next step" if world > 1 else ""),
+                       (", every step's records gathered on rank 0 through host shared memory (sharding.ShmGather), read one step behind" if world > 1 else ""),
                 "roofline": {"bound": "pcie-h2d", "achieved": e2e_gbs, "peak": h2d_gbs, "unit": "GB/s per GPU",
                              "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
                              "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},
@@ -914,7 +934,7 @@ def run_lk_gpu(args, rank, world, local, with_cpu):
         "e2e": {"value": e2e_v, "unit": "frame-pairs/s",
                 "h2d_bytes_per_step": fb + 4 * n, "d2h_bytes_per_step": (16 + 24) * n, "steps": e_steps,
                 "api": "aof_lk_calc_flow_batch (pinned host frames -> H2D -> kernels -> D2H)" +
-                       (", every step's records gathered on rank 0 over the host (gloo) group, one gather in flight under the next step" if world > 1 else ""),
+                       (", every step's records gathered on rank 0 through host shared memory (sharding.ShmGather), read one step behind" if world > 1 else ""),
                 "roofline": {"bound": "pcie-h2d", "achieved": e2e_gbs, "peak": h2d_gbs, "unit": "GB/s per GPU",
                              "frac": e2e_gbs / h2d_gbs if h2d_gbs else None,
                              "peak_source": "measured in this run: pinned host -> device copy, all ranks at once, slowest rank"}},

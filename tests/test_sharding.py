@@ -82,3 +82,46 @@ def test_shard_ranges_partition(pkg):
             for s in {0, total // 2, total - 1}:
                 r = sh.owner_of(s, total, world)
                 assert edges[r][0] <= s < edges[r][1]
+
+
+def shm_worker(rank, world, path, q):
+    sys.path.insert(0, ROOT)
+    import time
+    import __graft_entry__ as entry
+    sh = entry.load_package().sharding
+    if rank != 0:
+        while not os.path.exists(path + ".ready"):
+            time.sleep(0.01)
+    g = sh.ShmGather(path, TOTAL, world, rank, out_dtype, create=rank == 0)
+    if rank == 0:
+        open(path + ".ready", "w").close()
+    lo, hi = sh.shard_range(TOTAL, world, rank)
+    ok = True
+    for step in range(1, 40):
+        local = np.zeros(hi - lo, out_dtype)
+        local["quality"] = np.arange(lo, hi) + 1000 * step
+        local["flow_x"] = rank + step
+        g.put(local, step)
+        if rank == 0 and step >= 2:                      # one step in flight, as bench.py does
+            got = g.wait(step - 1)
+            ok = ok and np.array_equal(got["quality"], np.arange(TOTAL) + 1000 * (step - 1))
+            ok = ok and all(got["flow_x"][sh.shard_range(TOTAL, world, r)[0]] == r + step - 1 for r in range(world))
+    if rank == 0:
+        got = g.wait(39)
+        ok = ok and np.array_equal(got["quality"], np.arange(TOTAL) + 39000)
+        q.put(bool(ok))
+    g.close()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_shared_memory_gather(pkg, world, tmp_path):
+    path = str(tmp_path / "gather.bin")
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    procs = [ctx.Process(target=shm_worker, args=(r, world, path, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    assert q.get() is True
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
