@@ -106,7 +106,7 @@ class ShmGather:
                 f.truncate(nbytes)
         self.mm = np.memmap(path, dtype=np.uint8, mode="r+", shape=(nbytes,))
         self.seq = self.mm[: 64 * world].view(np.int64).reshape(world, 8)
-        self.buf = self.mm[64 * world:].view(self.dtype).reshape(2, total)
+        self.buf = self.mm[64 * world:].reshape(2, total * self.dtype.itemsize)   # bytes: numpy copies structured records field by field
         self.lo, self.hi = shard_range(total, world, rank)
         self.path = path
 
@@ -119,7 +119,8 @@ class ShmGather:
         while self.rank != 0 and int(self.seq[0, 1]) < step - 2:
             if time.monotonic() > t_end:
                 raise TimeoutError("ShmGather.put: step %d, rank 0 has read up to %d" % (step, int(self.seq[0, 1])))
-        self.buf[step & 1, self.lo:self.hi] = local
+        isz = self.dtype.itemsize
+        self.buf[step & 1, self.lo * isz:self.hi * isz] = np.ascontiguousarray(local).view(np.uint8).reshape(-1)
         self.seq[self.rank, 0] = step
 
     def wait(self, step, timeout_s=60.0):
@@ -132,7 +133,7 @@ class ShmGather:
         while int(self.seq[:, 0].min()) < step:
             if time.monotonic() > t_end:
                 raise TimeoutError("ShmGather: step %d, sequence numbers %s" % (step, self.seq[:, 0].tolist()))
-        out = self.buf[step & 1].copy()
+        out = self.buf[step & 1].copy().view(self.dtype)
         self.seq[0, 1] = step
         return out
 
